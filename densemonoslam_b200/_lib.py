@@ -1,0 +1,88 @@
+"""ctypes loader for the product library `lib/libdmsodom.so` (C ABI: include/dmsodom/odom_c.h).
+
+There is no fallback: if the CUDA library is missing this raises, it never routes to a CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libdmsodom.so")
+REPO_ROOT = os.path.dirname(_HERE)
+
+
+class DmsResult(C.Structure):
+    _fields_ = [("lastICPError", C.c_float), ("lastICPCount", C.c_float), ("lastRGBError", C.c_float),
+                ("lastRGBCount", C.c_float), ("lastSO3Error", C.c_float), ("lastSO3Count", C.c_float),
+                ("lastA", C.c_double * 36), ("lastb", C.c_double * 6), ("iters", C.c_int * 3), ("so3_iters", C.c_int)]
+
+
+class DmsTiming(C.Structure):
+    _fields_ = [("track_ms", C.c_float), ("so3Step_ms", C.c_float), ("computeRgbResidual_ms", C.c_float),
+                ("icpStep_ms", C.c_float), ("rgbStep_ms", C.c_float)]
+
+
+class DmsIterRecord(C.Structure):
+    _fields_ = [("level", C.c_int32), ("iter", C.c_int32), ("icp_count", C.c_int64), ("rgb_count", C.c_int64),
+                ("rgb_sigma", C.c_int64), ("icp", C.c_float * 28), ("rgb", C.c_float * 28), ("R", C.c_float * 9),
+                ("t", C.c_float * 3)]
+
+
+# every symbol declared in include/dmsodom/odom_c.h (tests check the header against this list)
+_P = C.c_void_p
+_F3 = C.POINTER(C.c_float)
+SIGNATURES = {
+    "dms_odom_create": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int] + [C.c_float] * 6),
+    "dms_odom_destroy": (C.c_int, [_P]),
+    "dms_odom_last_error": (C.c_char_p, [_P]),
+    "dms_odom_set_timing": (C.c_int, [_P, C.c_int]),
+    "dms_odom_get_timing": (C.c_int, [_P, C.POINTER(DmsTiming)]),
+    "dms_odom_init_icp_depth": (C.c_int, [_P, _P, C.c_size_t, C.c_float, _P]),
+    "dms_odom_init_icp_maps": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _P]),
+    "dms_odom_init_icp_model": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _F3, _P]),
+    "dms_odom_init_rgb": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_rgb_model": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_first_rgb": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_icp_depth_host": (C.c_int, [_P, _P, C.c_size_t, C.c_float, _P]),
+    "dms_odom_init_icp_maps_host": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _P]),
+    "dms_odom_init_icp_model_host": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _F3, _P]),
+    "dms_odom_init_rgb_host": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_rgb_model_host": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_first_rgb_host": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_track": (C.c_int, [_P, _F3, _F3, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.POINTER(DmsResult)]),
+    "dms_odom_track_async": (C.c_int, [_P, _F3, _F3, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "dms_odom_track_collect": (C.c_int, [_P, _F3, _F3, _P, C.POINTER(DmsResult)]),
+    "dms_odom_icp_residual": (C.c_int, [_P, _F3, _F3, _F3, _F3, C.POINTER(C.c_float), C.POINTER(C.c_int), _P]),
+    "dms_odom_get_covariance": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "dms_odom_get_buffer": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(_P), C.POINTER(C.c_size_t), C.POINTER(C.c_int),
+                                      C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "dms_odom_download": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_size_t, _P]),
+    "dms_odom_get_trace": (C.c_int, [_P, C.POINTER(DmsIterRecord), C.c_int, C.POINTER(C.c_int)]),
+    "dms_odom_icp_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P, _P]),
+    "dms_odom_rgb_residual": (C.c_int, [_P, C.c_int, _F3, _F3, C.POINTER(C.c_int64), C.POINTER(C.c_int64), _P]),
+    "dms_odom_rgb_step": (C.c_int, [_P, C.c_int, C.c_float, _F3, C.POINTER(C.c_int64), _P]),
+    "dms_odom_so3_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P]),
+    "dms_odom_compute_derivatives": (C.c_int, [_P, _P]),
+    "dms_version": (C.c_char_p, []),
+    "dms_device_count": (C.c_int, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libdmsodom.so and bind every entry point.  Raises if the library is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with densemonoslam_b200/csrc/build.sh "
+                "(or __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib

@@ -1,0 +1,73 @@
+// Host-visible launchers of the dmsodom kernels (internal to the library).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "common.cuh"
+#include "dmsodom/odom_c.h"
+
+namespace dms {
+
+// ---- pyramid.cu
+cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4, const float4* n4, int pitch4,
+                                const float* pose16_or_null, float* zdepth, float zcut, cudaStream_t s);
+cudaError_t launch_v2d_intensity(const float* zsrc, int pitch_z, float* depth, int pitch_d, const uchar4* rgba,
+                                 int pitch_rgba, unsigned char* img, int pitch_i, int rows, int cols, cudaStream_t s);
+cudaError_t launch_pyrdown_gauss(const float* sd, int spd, float* dd, int dpd, const unsigned char* si, int spi,
+                                 unsigned char* di, int dpi, int srows, int scols, cudaStream_t s);
+cudaError_t launch_pyrdown_u16(const unsigned short* src, int sp, unsigned short* dst, int dp, int srows, int scols,
+                               cudaStream_t s);
+cudaError_t launch_vmap_nmap(const Level* lv, float cutoff, cudaStream_t s);
+
+// ---- track.cu
+static const int ACC_STRIDE = 16;   // unsigned long long words between accumulator slots (128 B)
+static const int ACC_SLOTS = 192;
+static const int MAX_TRACE = 160;   // >= 3*50 interMap iterations
+
+// Device-resident control block of the persistent tracking kernel.
+struct Ctrl {
+  unsigned int arrive, gen, bad, pad0;
+  double resultRt[16];
+  double resultR[9], lastResultR[9];
+  float Rcurr[9], tcurr[3];
+  float krkinv[9], kt[3];
+  float sigma;
+  int brk, so3_done, n_trace;
+  float icp_vals[28];
+  long long icp_count, rgb_count, rgb_sigma;
+  float R_lr[9], so3_H[9], so3_kinv[9], so3_krlr[9];
+  float so3_lastError, so3_lastCount;
+  float lastRGBError, pad1;
+  unsigned long long t_so3, t_phaseA, t_phaseB, t_mark;  // ns spent per phase kind (Stopwatch keys)
+  dms_odom_result res;
+  float out_R[9], out_t[3];
+};
+
+struct TrackParams {
+  Level lv[3];
+  int rgbOnly, pyramid, fastOdom, so3, interMap, icp, rgb;
+  float icpWeight;
+  float Rprev[9], tprev[3], Rprev_inv[9];
+  float distThres, angleThres;
+  int iters[3];
+  Ctrl* ctrl;
+  unsigned long long* acc;
+  dms_iter_record* trace;
+  int timing;
+};
+
+int track_max_grid(int device, int* block_threads);  // co-resident CTAs for the cooperative launch
+cudaError_t launch_track(const TrackParams& p, int grid, cudaStream_t s);
+
+// single-step operators (regular launches + finalize)
+struct StepOut { float vals[28]; long long count, count2, sigma; int bad; int pad; };
+cudaError_t launch_derivatives(const Level* lv, cudaStream_t s);
+cudaError_t launch_icp_step(const Level& lv, const float Rcurr[9], const float tcurr[3], const float Rprev_inv[9],
+                            const float tprev[3], float distThres, float angleThres, unsigned long long* acc, StepOut* d_out,
+                            unsigned char* d_mask_or_null, int mask_pitch, cudaStream_t s);
+cudaError_t launch_rgb_residual(const Level& lv, const float kt[3], const float krkinv[9], unsigned long long* acc,
+                                StepOut* d_out, cudaStream_t s);
+cudaError_t launch_rgb_step(const Level& lv, float sigma, unsigned long long* acc, StepOut* d_out, cudaStream_t s);
+cudaError_t launch_so3_step(const Level& lv, const float H[9], const float kinv[9], const float krlr[9],
+                            unsigned long long* acc, StepOut* d_out, cudaStream_t s);
+
+}  // namespace dms

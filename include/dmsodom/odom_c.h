@@ -1,0 +1,171 @@
+/*
+ * dmsodom C ABI -- B200-native (sm_100a) dense RGB-D odometry.
+ *
+ * Drop-in boundary for the tracking hot path of robotvisionmu/DenseMonoSLAM
+ * (ElasticFusion's RGBDOdometry).  Each entry point names the reference interface it
+ * replaces; paths are relative to elasticfusion/Core/src/ in the reference tree:
+ *   RO.h / RO.cpp = Utils/RGBDOdometry.{h,cpp},  cf.cuh = Cuda/cudafuncs.cuh,
+ *   reduce.cu = Cuda/reduce.cu,  cf.cu = Cuda/cudafuncs.cu
+ *
+ * Conventions
+ *  - plain C types only; every pointer named d_* is a DEVICE pointer on the handle's
+ *    device, every pointer named h_* / unprefixed small array is HOST memory.
+ *  - `stream` is a cudaStream_t passed as void* (0 = default stream).  Work is enqueued on
+ *    it; entry points that return results to host memory synchronise that stream before
+ *    returning (the reference synchronises the whole device at the same places).
+ *  - all functions return 0 on success, a negative dms_status or a positive cudaError_t
+ *    otherwise, and never call exit() (the reference's cudaSafeCall prints and exit(0)s,
+ *    convenience.cuh:64-71).  dms_odom_last_error() gives the message.
+ *  - one handle = one device = one host thread at a time.  Distinct handles are
+ *    independent (one tracker per sensor / per GPU).
+ *  - the GL textures of the reference (GPUTexture*, RO.h:47-66) are replaced by headless
+ *    device buffers: RGBA8 colour, R16UI depth in millimetres, RGBA32F vertex / normal
+ *    maps, row pitch in bytes.
+ */
+#ifndef DMSODOM_ODOM_C_H_
+#define DMSODOM_ODOM_C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dms_odom dms_odom;
+
+enum dms_status {
+  DMS_OK = 0,
+  DMS_ERR_INVALID = -1,   /* bad argument */
+  DMS_ERR_NOMEM = -2,     /* device allocation failed */
+  DMS_ERR_DEVICE = -3,    /* device lacks a required capability (cooperative launch, sm_100) */
+  DMS_ERR_TOO_LARGE = -4  /* size beyond a stated maximum */
+};
+
+/* Public state of RGBDOdometry after getIncrementalTransformation (RO.h:70-77) plus the
+ * iteration counts actually run. */
+typedef struct dms_odom_result {
+  float lastICPError, lastICPCount, lastRGBError, lastRGBCount, lastSO3Error, lastSO3Count;
+  double lastA[36]; /* row-major 6x6 */
+  double lastb[6];
+  int iters[3];     /* GN iterations run at pyramid level 0,1,2 */
+  int so3_iters;    /* so3Step evaluations */
+} dms_odom_result;
+
+/* Stopwatch keys of the reference (RO.cpp:336,444,495,525), filled from CUDA events when
+ * timing is enabled with dms_odom_set_timing(); milliseconds of the last track call. */
+typedef struct dms_odom_timing {
+  float track_ms;   /* whole getIncrementalTransformation on the device */
+  float so3Step_ms, computeRgbResidual_ms, icpStep_ms, rgbStep_ms; /* estimated split by phase cycle counters */
+} dms_odom_timing;
+
+/* ---- lifetime: RGBDOdometry::RGBDOdometry / ~RGBDOdometry (RO.cpp:21-116).
+ * NOTE the argument order cx, cy, fx, fy of the reference constructor (RO.h:34-36).
+ * All device buffers are allocated here once and zero-filled. */
+int dms_odom_create(dms_odom** out, int device, int width, int height, float cx, float cy, float fx, float fy,
+                    float distThresh, float angleThresh);
+int dms_odom_destroy(dms_odom* h);
+const char* dms_odom_last_error(const dms_odom* h);
+int dms_odom_set_timing(dms_odom* h, int enabled);
+int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
+
+/* ---- pyramid construction.
+ * initICP(GPUTexture* filteredDepth, depthCutoff, stream)           RO.cpp:118-142 */
+int dms_odom_init_icp_depth(dms_odom* h, const uint16_t* d_depth, size_t pitch_bytes, float depthCutoff, void* stream);
+/* initICP(GPUTexture* predictedVertices, predictedNormals, cutoff)  RO.cpp:144-167 */
+int dms_odom_init_icp_maps(dms_odom* h, const float* d_vertices4, const float* d_normals4, size_t pitch_bytes,
+                           float depthCutoff, void* stream);
+/* initICPModel(vertices, normals, cutoff, Eigen::Matrix4f modelPose) RO.cpp:169-207;
+ * pose is the row-major 4x4 camera->global transform. */
+int dms_odom_init_icp_model(dms_odom* h, const float* d_vertices4, const float* d_normals4, size_t pitch_bytes,
+                            float depthCutoff, const float pose_rowmajor[16], void* stream);
+/* initRGB / initRGBModel / initFirstRGB(GPUTexture* rgb)             RO.cpp:238-266.
+ * As in the reference, the depth pyramid paired with the image comes from the vertex map
+ * loaded by the LAST init_icp_maps / init_icp_model call (RO.cpp:213,240,246). */
+int dms_odom_init_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, void* stream);
+int dms_odom_init_rgb_model(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, void* stream);
+int dms_odom_init_first_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, void* stream);
+
+/* Same five calls with HOST buffers (dense rows unless pitch given); the copy to the device
+ * is part of the call.  Used by callers without a device-side producer and by bench.py's
+ * end-to-end number. */
+int dms_odom_init_icp_depth_host(dms_odom* h, const uint16_t* h_depth, size_t pitch_bytes, float depthCutoff, void* stream);
+int dms_odom_init_icp_maps_host(dms_odom* h, const float* h_vertices4, const float* h_normals4, size_t pitch_bytes,
+                                float depthCutoff, void* stream);
+int dms_odom_init_icp_model_host(dms_odom* h, const float* h_vertices4, const float* h_normals4, size_t pitch_bytes,
+                                 float depthCutoff, const float pose_rowmajor[16], void* stream);
+int dms_odom_init_rgb_host(dms_odom* h, const uint8_t* h_rgba, size_t pitch_bytes, void* stream);
+int dms_odom_init_rgb_model_host(dms_odom* h, const uint8_t* h_rgba, size_t pitch_bytes, void* stream);
+int dms_odom_init_first_rgb_host(dms_odom* h, const uint8_t* h_rgba, size_t pitch_bytes, void* stream);
+
+/* ---- the tracker: getIncrementalTransformation(trans, rot, rgbOnly, icpWeight, pyramid,
+ * fastOdom, so3, interMap, stream)  RO.cpp:268-605.  trans[3] / rot_rowmajor[9] carry the
+ * previous pose in and the refined pose out.  The whole SO(3) + 3-level Gauss-Newton loop,
+ * including the 6x6 solves and pose updates, runs on the device in one launch; `out`
+ * (optional) receives the public fields.  Synchronises `stream`. */
+int dms_odom_track(dms_odom* h, float trans[3], float rot_rowmajor[9], int rgbOnly, float icpWeight, int pyramid,
+                   int fastOdom, int so3, int interMap, void* stream, dms_odom_result* out);
+/* Asynchronous pair for pipelined callers: enqueue, then collect later. */
+int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot_rowmajor[9], int rgbOnly, float icpWeight,
+                         int pyramid, int fastOdom, int so3, int interMap, void* stream);
+int dms_odom_track_collect(dms_odom* h, float trans[3], float rot_rowmajor[9], void* stream, dms_odom_result* out);
+
+/* getICPResidual(trans_curr, rot_curr, trans_prev, rot_prev, icpError, icpCount)  RO.cpp:612-643
+ * (deterministic here; the reference's icpRes uses float atomicAdd, reduce.cu:482-540). */
+int dms_odom_icp_residual(dms_odom* h, const float trans_curr[3], const float rot_curr[9], const float trans_prev[3],
+                          const float rot_prev[9], float* icpError, int* icpCount, void* stream);
+/* getCovariance() = lastA.lu().inverse()  RO.cpp:607-610 (host, 6x6 double) */
+int dms_odom_get_covariance(const dms_odom* h, double cov_rowmajor[36]);
+
+/* ---- buffer accessors: nextImg / lastImg / nextD / lastVmap (RO.h:79-90) and the rest of
+ * the pyramid state for inspection.  Planar maps are 3*rows x cols floats (x-plane rows,
+ * then y, then z; RO.cpp:97-101), pitched. */
+enum dms_buffer {
+  DMS_BUF_VMAP_CURR = 0, DMS_BUF_NMAP_CURR = 1, DMS_BUF_VMAP_G_PREV = 2, DMS_BUF_NMAP_G_PREV = 3,
+  DMS_BUF_LAST_DEPTH = 4, DMS_BUF_NEXT_DEPTH = 5, DMS_BUF_LAST_IMAGE = 6, DMS_BUF_NEXT_IMAGE = 7,
+  DMS_BUF_LAST_NEXT_IMAGE = 8, DMS_BUF_DIDX = 9, DMS_BUF_DIDY = 10, DMS_BUF_DEPTH_TMP = 11,
+  DMS_BUF_CORRES = 12 /* 8-byte records {i16 u0, i16 v0, i16 diff, u8 valid, u8 0}: compact DataTerm, types.cuh:76-82 */
+};
+int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t* pitch_bytes, int* rows, int* cols,
+                        int* elem_bytes);
+/* Copies a buffer to dense host memory (rows*cols*elem_bytes, planar maps 3 planes). */
+int dms_odom_download(dms_odom* h, int which, int level, void* h_dst, size_t dst_bytes, void* stream);
+
+/* Per-iteration trace of the last track call (for parity tests): record i holds
+ * {level, iter, icp_inliers, rgb_count, rgb_sigma} and the 28 ICP / 28 RGB reduced values
+ * (27 products in JtJJtrSE3 order, types.cuh:117-131, then residual) and the pose after it. */
+typedef struct dms_iter_record {
+  int32_t level, iter;
+  int64_t icp_count, rgb_count, rgb_sigma;
+  float icp[28], rgb[28];
+  float R[9], t[3];
+} dms_iter_record;
+int dms_odom_get_trace(dms_odom* h, dms_iter_record* h_records, int max_records, int* n_records);
+
+/* ---- single-step operators: the free functions of cudafuncs.cuh that RGBDOdometry (and
+ * MutualInformation / KeyFrame / FGROdometry) call.  They act on the handle's pyramid
+ * level `level` and return the reduced values to the host, like the reference wrappers do.
+ * out28: 27 products + residual; counts are exact integers.
+ * icpStep            reduce.cu:367-428 */
+int dms_odom_icp_step(dms_odom* h, int level, const float Rcurr[9], const float tcurr[3], const float Rprev_inv[9],
+                      const float tprev[3], float out28[28], int64_t* inliers, uint8_t* h_mask_or_null, void* stream);
+/* computeRgbResidual reduce.cu:865-925 (writes DMS_BUF_CORRES of that level) */
+int dms_odom_rgb_residual(dms_odom* h, int level, const float kt[3], const float krkinv[9], int64_t* count,
+                          int64_t* sigma, void* stream);
+/* rgbStep            reduce.cu:643-685 (reads DMS_BUF_CORRES) */
+int dms_odom_rgb_step(dms_odom* h, int level, float sigma, float out28[28], int64_t* count, void* stream);
+/* so3Step            reduce.cu:1054-1103 (lastNextImage vs nextImage of `level`) */
+int dms_odom_so3_step(dms_odom* h, int level, const float imageBasis[9], const float kinv[9], const float krlr[9],
+                      float out10[10], int64_t* count, void* stream);
+/* computeDerivativeImages cf.cu:697-725 on nextImage of every level (also refreshes the
+ * iteration-invariant photometric candidate mask used by rgb_residual). */
+int dms_odom_compute_derivatives(dms_odom* h, void* stream);
+
+/* ---- library info */
+const char* dms_version(void);
+int dms_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMSODOM_ODOM_C_H_ */

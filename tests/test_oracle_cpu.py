@@ -1,0 +1,142 @@
+"""CPU-only tests of the oracle (oracle/cpu_odom.cpp): hand-checked quirks of the reference kernels,
+self-consistency of the full track, and invariance of the canonical reduction to threading."""
+import fractions
+
+import numpy as np
+
+from conftest import small_cam
+
+
+def f32(x):
+    return np.float32(x)
+
+
+def fma32(a, b, c):
+    """Correctly rounded fp32 fma via exact rationals."""
+    r = fractions.Fraction(float(a)) * fractions.Fraction(float(b)) + fractions.Fraction(float(c))
+    return np.float32(float(r))  # double rounding is harmless here: products of <=8-bit ints by fp32 constants
+
+
+def test_intensity_matches_reference_expression(orc):
+    # cf.cu:651-654: int v = x*0.114f + y*0.299f + z*0.587f  ->  fma(z,.587, fma(x,.114, y*.299)), truncated
+    rng = np.random.RandomState(0)
+    rgba = rng.randint(0, 256, size=(64, 64, 4)).astype(np.uint8)
+    rgba[0, 0] = (255, 255, 255, 255); rgba[0, 1] = (0, 0, 0, 0); rgba[0, 2] = (1, 1, 1, 9)
+    out = orc.bgr_to_intensity(rgba)
+    for (y, x) in [(0, 0), (0, 1), (0, 2)] + [tuple(rng.randint(0, 64, 2)) for _ in range(300)]:
+        r, g, b, _ = [f32(v) for v in rgba[y, x]]
+        t = f32(g * f32(0.299))
+        v = fma32(b, f32(0.587), fma32(r, f32(0.114), t))
+        assert out[y, x] == int(v), (y, x)
+    assert out[0, 0] == 255 and out[0, 1] == 0
+
+
+def test_pyrdown_u8_edge_quirks(orc):
+    # exclusive upper bound min(2x+3, cols-1): the last source column/row is never read,
+    # and weights are indexed from the window end.
+    src = np.full((8, 8), 100, np.uint8)
+    src[:, -1] = 255; src[-1, :] = 255
+    out = orc.pyrdown_u8_gauss(src)
+    assert out.shape == (4, 4) and (out == 100).all()
+    # zero taps are skipped, all-zero window -> 0
+    z = np.zeros((8, 8), np.uint8)
+    assert (orc.pyrdown_u8_gauss(z) == 0).all()
+    z[2, 2] = 77
+    o = orc.pyrdown_u8_gauss(z)
+    assert o[1, 1] == 77 and o[0, 0] == 77 and o[3, 3] == 0
+
+
+def test_pyrdown_f32_nan_handling(orc):
+    src = np.full((8, 8), 2.0, np.float32)
+    src[0:4, 0:4] = np.nan
+    out = orc.pyrdown_f32_gauss(src)
+    assert np.isnan(out[0, 0]) and out[3, 3] == 2.0 and out[1, 1] == 2.0
+
+
+def test_pyrdown_u16_bilateral(orc):
+    src = np.full((8, 8), 1000, np.uint16)
+    src[0, 1] = 2000  # differs by >= 90 from the centre -> excluded
+    out = orc.pyrdown_u16(src)
+    assert (out == 1000).all()
+    src[:] = 0
+    assert (orc.pyrdown_u16(src) == 0).all()
+
+
+def test_derivative_border_quirk(orc):
+    # interior = true convolution with the flipped 3x3; cf.cu:684-690
+    img = np.zeros((5, 6), np.uint8)
+    img[:, 3:] = 100
+    dx, dy = orc.derivatives(img)
+    g = [0.52201, 0.79451, 0.52201]
+    assert dx[2, 2] == int(np.float32(100) * np.float32(g[0] + g[1] + g[2]) * 1.0000001) or abs(int(dx[2, 2]) - 183) <= 1
+    assert dy[2, 2] == 0
+    assert dx[2, 0] == 0
+
+
+def test_vmap_nmap_and_resize(orc, synth):
+    cam = small_cam(synth, 4)
+    depth = np.full((cam.height, cam.width), 1500, np.uint16)
+    depth[10, 10] = 0
+    v = orc.create_vmap(depth, cam.fx, cam.fy, cam.cx, cam.cy, 25.0)
+    assert np.isnan(v[0, 10, 10]) and v[2, 5, 5] == np.float32(1.5)
+    n = orc.create_nmap(v)
+    assert np.isnan(n[0, -1, 0]) and np.isnan(n[0, 0, -1]) and np.isnan(n[0, 10, 9]) and np.isnan(n[0, 9, 10])
+    assert abs(abs(n[2, 5, 5]) - 1.0) < 1e-6
+    r = orc.resize_map(v, False)
+    assert r.shape == (3, cam.height // 2, cam.width // 2) and np.isnan(r[0, 5, 5]) and r[2, 0, 0] == np.float32(1.5)
+
+
+def _track(orc, cam, model, live, flags, threads=None):
+    if threads:
+        orc.set_num_threads(threads)
+    o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    pose = np.eye(4, dtype=np.float32)
+    o.initFirstRGB(model["rgba"])
+    o.initICPModel(model["vmap4"], model["nmap4"], pose); o.initRGBModel(model["rgba"])
+    o.initICP(live["depth"], 25.0); o.initRGB(live["rgba"])
+    t, R, res = o.getIncrementalTransformation(np.zeros(3), np.eye(3), *flags)
+    return t, R, res, o.log()
+
+
+def test_track_recovers_rendered_motion(orc, synth, pair_small):
+    cam, model, live, T = pair_small
+    t, R, res, log = _track(orc, cam, model, live, (False, 10.0, True, False, True, False))
+    assert list(res.iters) == [10, 5, 4]
+    assert np.max(np.abs(t - T[:3, 3])) < 6e-3, (t, T[:3, 3])
+    assert np.max(np.abs(R - T[:3, :3])) < 3e-3
+    assert res.lastICPCount > 0.5 * cam.width * cam.height
+    # identity motion -> (near) zero update
+    t0, R0, _, _ = _track(orc, cam, model, {"depth": model["depth"], "rgba": model["rgba"]}, (False, 10.0, True, False, False, False))
+    assert np.max(np.abs(t0)) < 2e-3 and np.max(np.abs(R0 - np.eye(3))) < 2e-3
+
+
+def test_reduction_is_schedule_independent(orc, synth, pair_small):
+    """The exact fixed-point accumulation makes the sums independent of the thread count."""
+    cam, model, live, T = pair_small
+    flags = (False, 10.0, True, False, True, False)
+    n = orc.num_threads()
+    a = _track(orc, cam, model, live, flags, threads=1)
+    b = _track(orc, cam, model, live, flags, threads=max(2, n))
+    orc.set_num_threads(n)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    for x, y in zip(a[3], b[3]):
+        assert np.array_equal(x["icp"], y["icp"]) and np.array_equal(x["rgb"], y["rgb"]) and x["icp_count"] == y["icp_count"]
+
+
+def test_flag_schedule(orc, synth, pair_small):
+    cam, model, live, T = pair_small
+    # RO.cpp:387-389
+    assert list(_track(orc, cam, model, live, (False, 10.0, False, True, False, False))[2].iters) == [3, 0, 0]
+    assert list(_track(orc, cam, model, live, (False, 10.0, False, False, False, False))[2].iters) == [10, 0, 0]
+    r = _track(orc, cam, model, live, (False, 100.0, True, False, False, True))[2]
+    assert list(r.iters) == [50, 50, 50] and r.lastRGBCount == 0
+    r = _track(orc, cam, model, live, (True, 10.0, True, False, True, False))[2]
+    assert r.lastICPCount == 0 and r.lastRGBCount > 0 and all(i <= n for i, n in zip(r.iters, (10, 5, 4)))
+
+
+def test_guard_rejects_large_translation(orc, synth):
+    # RO.cpp:589-593: |tcurr - tprev| > 0.3 m with an RGB term -> input pose returned
+    cam = small_cam(synth, 4)
+    model, live, T = synth.frame_pair(cam, seed=3, tvec=(0.9, 0.0, 0.0), rvec=(0, 0, 0))
+    t, R, res, _ = _track(orc, cam, model, live, (False, 10.0, True, False, False, False))
+    assert np.linalg.norm(t) <= 0.3 + 1e-6
