@@ -1,0 +1,312 @@
+#!/usr/bin/env python
+"""Benchmark of the dense tracking hot path (BASELINE.json metric: odometry frames/s).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload kitti|vga|1080p|fast]
+
+A step = one tracked frame of the named workload: initICPModel + initRGBModel + initICP(depth) +
+initRGB + getIncrementalTransformation (ICP+RGB, 3-level pyramid, icpWeight 10, SO(3) on), i.e. the
+call sequence of ElasticFusion::processFrame (EF.cpp:173-201).  Default workload = BASELINE.json
+configs[1]: KITTI shape 1241x376, synthetic forward-driving sequence, open loop.
+
+`value`     frames/s with the frame inputs already resident in HBM (a ring of distinct frames
+            larger than L2), timed with CUDA events on the launching stream.
+`e2e`       the same through the host-buffer C-ABI entry points (pinned host inputs, H2D copies and
+            the D2H result read inside the timed region).
+`roofline`  the tracking kernel k_track: algorithmic bytes per launch / mean launch duration
+            (CUDA events around each launch, recorded inside the timed region).
+`cpu_baseline` / --impl reference: the CPU oracle (an OpenMP transcription of the reference's
+            equations - the reference has no CPU implementation of this path) on the host cores.
+N > 1 (torchrun): one independent sensor sequence per GPU (the collaborative --n mode maps one
+tracker per GPU); no data-path collective; value = frames of all ranks / max-over-ranks time.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLAGS = dict(rgbOnly=False, icpWeight=10.0, pyramid=True, fastOdom=False, so3=True)
+
+
+def workload_def(name):
+    from densemonoslam_b200 import synth
+    if name == "kitti":
+        return synth.CAM_KITTI, "KITTI-shape 1241x376 synthetic sequence, ICP+RGB, 3-level pyramid, so3 on, open loop (configs[1])"
+    if name == "vga":
+        return synth.CAM_VGA, "640x480 synthetic RGB-D pair sequence, ICP+RGB, 3-level pyramid, icpWeight=10, so3 on (configs[0])"
+    if name == "1080p":
+        return synth.CAM_1080P, "1920x1080 synthetic RGB-D stress sequence, full pyramid (configs[3])"
+    if name == "fast":
+        return synth.CAM_VGA, "640x480 fast odometry (single level, 3 iterations) (configs[2])"
+    raise SystemExit(f"unknown workload {name}")
+
+
+def make_frames(name, cam, n, seed):
+    """n distinct frames: model buffers rendered at the prior pose, live buffers at the GT pose."""
+    from densemonoslam_b200 import synth
+    if name == "kitti":
+        return synth.kitti_sequence(cam, n, seed=seed)
+    scene = synth.room_scene(seed)
+    frames = []
+    rng = np.random.RandomState(seed)
+    T = np.eye(4)
+    for f in range(n):
+        T = T @ synth.pose_from(rng.randn(3) * 0.004, rng.randn(3) * 0.006)
+        prior = T @ synth.pose_from(rng.randn(3) * 0.006, rng.randn(3) * 0.01)
+        model = synth.render(scene, cam, prior, seed=seed + 2 * f, hole_frac=0.0)
+        live = synth.render(scene, cam, T, seed=seed + 2 * f + 1)
+        frames.append({"model": model, "live": live, "prior": prior.astype(np.float32), "gt": T.astype(np.float32)})
+    return frames
+
+
+def level_pixels(cam):
+    return [(cam.height >> l) * (cam.width >> l) for l in range(3)]
+
+
+def algorithmic_bytes(cam, iters, so3_iters):
+    """62 B per pixel per fused ICP+RGB GN iteration (48 ICP + 14 RGB), 2 B per pixel
+    per so3 evaluation (level 2), derivative images 1 B read + 4 B written per pixel of every level."""
+    n = level_pixels(cam)
+    gn = sum(62 * n[l] * iters[l] for l in range(3))
+    so3 = 2 * n[2] * so3_iters
+    der = 5 * sum(n)
+    return gn + so3 + der
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def result(self):
+        self.stop_flag = True
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def run_oracle_frames(cam, frames, n_frames, budget_s, threads=None):
+    """Times the CPU oracle on the same per-frame call sequence; returns (frames_done, seconds, threads)."""
+    from oracle import oracle as orc
+    if threads:
+        orc.set_num_threads(threads)
+    o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    o.initFirstRGB(frames[0]["live"]["rgba"])
+    done, t0 = 0, time.perf_counter()
+    while done < n_frames:
+        f = frames[done % len(frames)]
+        p = f["prior"]
+        o.initICPModel(f["model"]["vmap4"], f["model"]["nmap4"], p)
+        o.initRGBModel(f["model"]["rgba"])
+        o.initICP(f["live"]["depth"], 25.0)
+        o.initRGB(f["live"]["rgba"])
+        o.getIncrementalTransformation(p[:3, 3].copy(), p[:3, :3].copy(), FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"],
+                                       FLAGS["fastOdom"], FLAGS["so3"], keepLog=False)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    return done, time.perf_counter() - t0, orc.num_threads()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="kitti")
+    ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cam, wl_desc = workload_def(args.workload)
+    if args.workload == "fast":
+        FLAGS.update(pyramid=False, fastOdom=True)
+    iters_nominal = [3 if FLAGS["fastOdom"] else 10, 5 if FLAGS["pyramid"] else 0, 4 if FLAGS["pyramid"] else 0]
+    config = {"workload": wl_desc, "width": cam.width, "height": cam.height, "icpWeight": FLAGS["icpWeight"], "iterations": iters_nominal,
+              "so3": FLAGS["so3"], "parallelism": f"{world} independent sensor tracker(s), one per GPU, no collective on the path"}
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        frames = make_frames(args.workload, cam, min(args.ring, 4), seed=2021)
+        run_oracle_frames(cam, frames, max(1, min(args.warmup, 2)), 30.0)
+        done, secs, threads = run_oracle_frames(cam, frames, args.steps, 150.0)
+        fps = done / secs
+        sample = f"{done} of {args.steps} frames (time-bounded), same per-frame call sequence"
+        print(json.dumps({
+            "impl": "reference", "metric": "odometry_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference has no CPU implementation of this path; this is the OpenMP transcription of its equations (oracle/cpu_odom.cpp)"}))
+        return
+
+    # ------------------------------------------------------------------ our arm (GPU)
+    import torch
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from densemonoslam_b200.odometry import RGBDOdometry
+    from densemonoslam_b200 import _lib
+
+    ring = max(2, args.ring)
+    frames = make_frames(args.workload, cam, ring, seed=2021 + 1000 * rank)  # each rank = its own sensor
+    per_frame_in = sum(frames[0][k][b].nbytes for k, b in (("model", "vmap4"), ("model", "nmap4"), ("model", "rgba"), ("live", "depth"), ("live", "rgba")))
+    dev = []
+    pinned = []
+    for f in frames:
+        d = {"v": torch.from_numpy(f["model"]["vmap4"]).cuda(), "n": torch.from_numpy(f["model"]["nmap4"]).cuda(),
+             "mi": torch.from_numpy(f["model"]["rgba"]).cuda(), "d": torch.from_numpy(f["live"]["depth"]).cuda(),
+             "li": torch.from_numpy(f["live"]["rgba"]).cuda()}
+        dev.append(d)
+        pinned.append({k: torch.from_numpy(a).pin_memory() for k, a in (("v", f["model"]["vmap4"]), ("n", f["model"]["nmap4"]),
+                                                                          ("mi", f["model"]["rgba"]), ("d", f["live"]["depth"]), ("li", f["live"]["rgba"]))})
+    config["ring_frames"] = ring
+    config["cache"] = f"inputs cycle through {ring} distinct resident frames = {ring * per_frame_in / 1e6:.0f} MB (> 126 MB L2)"
+
+    odo = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
+    odo.set_timing(True)
+    stream = torch.cuda.current_stream()
+    odo.initFirstRGB(dev[0]["li"], stream=stream)
+
+    def step_device(i):
+        f, d = frames[i % ring], dev[i % ring]
+        p = f["prior"]
+        odo.initICPModel(d["v"], d["n"], 25.0, p, stream=stream)
+        odo.initRGBModel(d["mi"], stream=stream)
+        odo.initICP(d["d"], 25.0, stream=stream)
+        odo.initRGB(d["li"], stream=stream)
+        return odo.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
+                                                FLAGS["so3"], stream=stream)
+
+    def step_host(i):
+        f, h = frames[i % ring], pinned[i % ring]
+        p = f["prior"]
+        odo.initICPModel(h["v"].numpy(), h["n"].numpy(), 25.0, p, stream=stream)
+        odo.initRGBModel(h["mi"].numpy(), stream=stream)
+        odo.initICP(h["d"].numpy(), 25.0, stream=stream)
+        odo.initRGB(h["li"].numpy(), stream=stream)
+        return odo.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
+                                                FLAGS["so3"], stream=stream)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps, warmup, collect_kernel_times):
+        for i in range(max(3, warmup)):
+            step_fn(i)
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ktimes, iters_seen, so3_seen = [], [], []
+        ev0.record(stream)
+        for i in range(steps):
+            step_fn(i)
+            if collect_kernel_times:
+                ktimes.append(odo.timing()["track"])
+                iters_seen.append(list(odo.iters)); so3_seen.append(odo.so3_iters)
+        ev1.record(stream)
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clocks = sampler.result()
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, ktimes, iters_seen, so3_seen, clocks
+
+    ms, ktimes, iters_seen, so3_seen, clocks = timed(step_device, args.steps, args.warmup, True)
+    value = world * args.steps / (ms * 1e-3)
+    t_last, R_last = step_device(args.steps - 1)
+    gt = frames[(args.steps - 1) % ring]["gt"]
+    pose_err = float(np.max(np.abs(t_last - gt[:3, 3])))
+
+    e2e_steps = min(args.steps, 300)
+    ms_e2e, _, _, _, _ = timed(step_host, e2e_steps, min(args.warmup, 5), False)
+    e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
+
+    # roofline of the dominant kernel (k_track)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))["hbm_gbs"]); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak = 6650.0; peak_src = "fallback (B200_PROFILING.md)"
+    k_ms = float(np.mean(ktimes))
+    alg = float(np.mean([algorithmic_bytes(cam, it, s3) for it, s3 in zip(iters_seen, so3_seen)]))
+    achieved = alg / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_track (persistent cooperative: derivatives + SO3 + 3-level GN incl. solves)", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (ms / args.steps),
+                "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
+
+    out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": config, "roofline": roofline,
+           "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in, "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
+                   "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
+           "gpu_launches": 11 * args.steps, "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
+           "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        host_frames = frames[: min(ring, 4)]
+        run_oracle_frames(cam, host_frames, 1, 30.0)
+        done, secs, threads = run_oracle_frames(cam, host_frames, 400, 15.0)
+        out["cpu_baseline"] = {"value": done / secs, "unit": "frames/s", "cores": threads, "kind": "port",
+                               "sample": f"{done} frames of the same workload in {secs:.1f} s (OpenMP oracle, all host threads)"}
+        done1, secs1, _ = run_oracle_frames(cam, host_frames, 40, 6.0, threads=1)
+        out["cpu_baseline"]["single_thread_value"] = done1 / secs1
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -66,6 +66,7 @@ SIGNATURES = {
     "dms_odom_compute_derivatives": (C.c_int, [_P, _P]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
+    "dms_track_d2h_bytes": (C.c_size_t, []),
 }
 
 _lib = None

@@ -114,6 +114,8 @@ int dms_device_count(void) {
   return n;
 }
 
+size_t dms_track_d2h_bytes(void) { return sizeof(Ctrl); }
+
 const char* dms_odom_last_error(const dms_odom* h) { return h ? h->err.c_str() : "null handle"; }
 
 int dms_odom_create(dms_odom** out, int device, int width, int height, float cx, float cy, float fx, float fy, float distThresh,
@@ -176,6 +178,13 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   for (int r = 0; r < nreq; ++r) { *reqs[r].p = h->slab + off; off += align_up(reqs[r].bytes, 256); }
   if (e == cudaSuccess) e = cudaMallocHost(&h->h_ctrl, sizeof(Ctrl));
   if (e == cudaSuccess) e = cudaMallocHost(&h->h_step, sizeof(StepOut));
+  if (e == cudaSuccess) {
+    // the public fields live in the device control block between calls (a call that skips SO(3) leaves
+    // lastSO3Error/Count untouched, like the reference's members); seed them as RO.cpp:26-31 does
+    memset(h->h_ctrl, 0, sizeof(Ctrl));
+    h->h_ctrl->res = h->last;
+    e = cudaMemcpy(h->ctrl, h->h_ctrl, sizeof(Ctrl), cudaMemcpyHostToDevice);
+  }
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -346,7 +355,9 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
   cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
   if (e != cudaSuccess) {
     // a failed launch leaves the barrier words undefined: rearm them
-    cudaMemset(h->ctrl, 0, sizeof(Ctrl));
+    memset(h->h_ctrl, 0, sizeof(Ctrl));
+    h->h_ctrl->res = h->last;
+    cudaMemcpy(h->ctrl, h->h_ctrl, sizeof(Ctrl), cudaMemcpyHostToDevice);
     cudaMemset(h->acc, 0, (size_t)ACC_SLOTS * ACC_STRIDE * sizeof(unsigned long long));
     return fail(h, (int)e, "k_track");
   }

@@ -68,8 +68,9 @@ class Scene:
         self.tex_scale = tex_scale
         self.seed = seed
 
-    def intersect(self, o, d):
-        """o [3], d [...,3] unit rays -> (t, normal) nearest hit, t=inf where none."""
+    def intersect(self, o, d, forward=None, max_range=None):
+        """o [3], d [...,3] unit rays -> (t, normal) nearest hit, t=inf where none.
+        `forward`/`max_range` let boxes behind the camera or out of range be skipped."""
         shape = d.shape[:-1]
         best_t = np.full(shape, np.inf)
         best_n = np.zeros(shape + (3,))
@@ -95,6 +96,12 @@ class Scene:
             nn = (p - c) / r
             best_n = np.where(ok[..., None], nn, best_n)
         for lo, hi in self.boxes:
+            if forward is not None:
+                c = 0.5 * (lo + hi) - o
+                rad = 0.5 * np.linalg.norm(hi - lo)
+                along = float(c @ forward)
+                if along + rad < 0 or (max_range is not None and along - rad > max_range):
+                    continue
             with np.errstate(divide="ignore", invalid="ignore"):
                 t0 = (lo - o) / d
                 t1 = (hi - o) / d
@@ -142,17 +149,17 @@ def room_scene(seed=0) -> Scene:
 
 
 def street_scene(seed=0) -> Scene:
-    """KITTI-like corridor: ground plane, two walls, boxes; depths 2-40 m."""
-    planes = [((0, 1, 0), 1.65), ((1, 0, 0), -7.5), ((1, 0, 0), 8.5), ((0, 0, 1), 400.0)]
+    """KITTI-like street: ground plane, two walls, parked boxes on both sides; depths ~2-40 m."""
+    planes = [((0, 1, 0), 1.65), ((1, 0, 0), -6.0), ((1, 0, 0), 6.5), ((0, 0, 1), 4000.0)]
     boxes = []
     rng = np.random.RandomState(seed + 17)
-    for i in range(60):
-        z0 = 6.0 + i * 7.0 + rng.uniform(0, 3)
+    for i in range(400):
+        z0 = 2.0 + i * 4.5 + rng.uniform(0, 1.5)
         side = -1 if i % 2 == 0 else 1
-        x0 = side * rng.uniform(2.5, 5.5)
-        w, h, l = rng.uniform(1.0, 2.2), rng.uniform(1.0, 2.4), rng.uniform(1.5, 4.0)
+        x0 = side * rng.uniform(1.8, 3.2)
+        w, h, l = rng.uniform(1.2, 1.9), rng.uniform(1.3, 2.6), rng.uniform(2.5, 4.0)
         boxes.append(((x0 - w / 2, 1.65 - h, z0), (x0 + w / 2, 1.65, z0 + l)))
-    return Scene(planes=planes, boxes=boxes, tex_scale=2.5, seed=seed)
+    return Scene(planes=planes, boxes=boxes, tex_scale=8.0, seed=seed)
 
 
 def render(scene: Scene, cam: Camera, T_wc: np.ndarray, *, max_depth=50.0, seed=0, zero_frac=0.03, hole_frac=0.04,
@@ -166,7 +173,7 @@ def render(scene: Scene, cam: Camera, T_wc: np.ndarray, *, max_depth=50.0, seed=
     dirs_c_unit = dirs_c / zscale[..., None]
     R, t = T_wc[:3, :3], T_wc[:3, 3]
     d_w = dirs_c_unit @ R.T
-    tt, n_w = scene.intersect(t, d_w)
+    tt, n_w = scene.intersect(t, d_w, forward=R[:, 2], max_range=max_depth * 1.2)
     hit = np.isfinite(tt)
     tt_safe = np.where(hit, tt, 0.0)
     p_w = t + d_w * tt_safe[..., None]
@@ -196,7 +203,10 @@ def render(scene: Scene, cam: Camera, T_wc: np.ndarray, *, max_depth=50.0, seed=
 
     zz = z.copy()
     if depth_noise > 0:
-        zz = zz * (1.0 + depth_noise * rng.randn(H, W))
+        # predicted-depth style error: a smooth multiplicative bias field plus a little white noise
+        ph = rng.uniform(0, 2 * np.pi, 2)
+        bias = np.sin(u * (2 * np.pi / W) * 1.5 + ph[0]) * np.sin(v * (2 * np.pi / H) * 1.1 + ph[1])
+        zz = zz * (1.0 + depth_noise * bias + 0.1 * depth_noise * rng.randn(H, W))
     dmm = np.clip(np.rint(zz * 1000.0), 0, 65535)
     dmm[~hit] = 0
     if hole_frac > 0:
@@ -252,7 +262,7 @@ def frame_pair(cam: Camera, scene: Scene | None = None, *, seed=1234, rvec=(0.01
 
 
 def kitti_sequence(cam: Camera, n_frames: int, *, seed=2021, step=0.8, yaw_deg=0.2, prior_sigma_t=0.03, prior_sigma_r_deg=0.3,
-                   depth_noise=0.02):
+                   depth_noise=0.004):
     """Config-2 style sequence: forward driving through `street_scene`.
 
     Yields per frame: model buffers rendered at the perturbed prior pose, live buffers at the

@@ -164,6 +164,8 @@ int dms_odom_compute_derivatives(dms_odom* h, void* stream);
 /* ---- library info */
 const char* dms_version(void);
 int dms_device_count(void);
+/* bytes copied device->host by one dms_odom_track call (the control block with pose + public fields) */
+size_t dms_track_d2h_bytes(void);
 
 #ifdef __cplusplus
 }
