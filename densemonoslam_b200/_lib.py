@@ -29,6 +29,11 @@ class DmsIterRecord(C.Structure):
                 ("t", C.c_float * 3)]
 
 
+class DmsStepSums(C.Structure):
+    _fields_ = [("vals", C.c_float * 28), ("count", C.c_int64), ("reserved0", C.c_int64), ("reserved1", C.c_int64),
+                ("bad", C.c_int32), ("reserved2", C.c_int32)]
+
+
 # every symbol declared in include/dmsodom/odom_c.h (tests check the header against this list)
 _P = C.c_void_p
 _F3 = C.POINTER(C.c_float)
@@ -64,6 +69,8 @@ SIGNATURES = {
     "dms_odom_rgb_step": (C.c_int, [_P, C.c_int, C.c_float, _F3, C.POINTER(C.c_int64), _P]),
     "dms_odom_so3_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P]),
     "dms_odom_compute_derivatives": (C.c_int, [_P, _P]),
+    "dms_icp_step_noalloc": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                       _F3, _F3, _F3, _F3, C.c_float, C.c_float, _P, _P]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

@@ -161,6 +161,39 @@ int dms_odom_so3_step(dms_odom* h, int level, const float imageBasis[9], const f
  * iteration-invariant photometric candidate mask used by rgb_residual). */
 int dms_odom_compute_derivatives(dms_odom* h, void* stream);
 
+/* ---- allocation-free variant of the ICP step.  NO COUNTERPART IN THE REFERENCE.
+ *
+ * For callers that are not allowed to allocate device memory: a tracker hosted inside another
+ * engine's frame loop with a memory budget fixed at start-up, a real-time thread that cannot take
+ * cudaMalloc's implicit device-wide synchronisation, or a plug-in that only ever works on buffers it
+ * is handed.  It needs no handle: the caller passes the four planar maps (3*rows x cols floats each,
+ * x plane rows first, row pitch `pitch_bytes`, 16-byte aligned rows), the level intrinsics, the
+ * poses as in dms_odom_icp_step, and a DEVICE record `d_out` that receives the same 27 products +
+ * residual and the inlier count.  The work is enqueued on `stream`; nothing is copied to the host.
+ *
+ * The reduction's scratch (the exact-accumulator lines, 24 KB) is a static device array inside
+ * the library, present on every GPU that loads it until the process exits.  Consequences:
+ *  - the call performs no cudaMalloc / cudaFree and uses no allocating library routine;
+ *  - images above DMS_NOALLOC_MAX_PIXELS are refused with DMS_ERR_TOO_LARGE (and a line on stderr);
+ *  - all calls on one GPU share the array, which is cleared at the start of every call: two calls
+ *    whose GPU work overlaps (different streams, or different host threads) race on it and give
+ *    wrong sums -- serialise them;
+ *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *    with that device current); make that first call before starting any stream capture.
+ * Results are bit-identical to dms_odom_icp_step on the same inputs. */
+#define DMS_NOALLOC_MAX_PIXELS (1 << 24)
+typedef struct dms_step_sums {
+  float vals[28];     /* 27 products in JtJJtrSE3 order (types.cuh:117-131), then the squared residual */
+  int64_t count;      /* inliers */
+  int64_t reserved0, reserved1;
+  int32_t bad;        /* 1 if a partial sum was NaN / Inf / out of accumulator range: vals are NaN */
+  int32_t reserved2;
+} dms_step_sums;
+int dms_icp_step_noalloc(const float* d_vmap_curr, const float* d_nmap_curr, const float* d_vmap_g_prev,
+                         const float* d_nmap_g_prev, size_t pitch_bytes, int rows, int cols, float fx, float fy,
+                         float cx, float cy, const float Rcurr[9], const float tcurr[3], const float Rprev_inv[9],
+                         const float tprev[3], float distThresh, float angleThresh, dms_step_sums* d_out, void* stream);
+
 /* ---- library info */
 const char* dms_version(void);
 int dms_device_count(void);
