@@ -20,7 +20,8 @@ class DmsResult(C.Structure):
 
 class DmsTiming(C.Structure):
     _fields_ = [("track_ms", C.c_float), ("so3Step_ms", C.c_float), ("computeRgbResidual_ms", C.c_float),
-                ("icpStep_ms", C.c_float), ("rgbStep_ms", C.c_float)]
+                ("icpStep_ms", C.c_float), ("rgbStep_ms", C.c_float), ("prologue_ms", C.c_float), ("serial_so3_ms", C.c_float),
+                ("serial_a_ms", C.c_float), ("serial_b_ms", C.c_float)]
 
 
 class DmsIterRecord(C.Structure):
@@ -64,6 +65,7 @@ SIGNATURES = {
                                       C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "dms_odom_download": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_size_t, _P]),
     "dms_odom_get_trace": (C.c_int, [_P, C.POINTER(DmsIterRecord), C.c_int, C.POINTER(C.c_int)]),
+    "dms_odom_get_timeline": (C.c_int, [_P, C.POINTER(C.c_uint64), C.c_int, C.POINTER(C.c_int)]),
     "dms_odom_icp_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P, _P]),
     "dms_odom_rgb_residual": (C.c_int, [_P, C.c_int, _F3, _F3, C.POINTER(C.c_int64), C.POINTER(C.c_int64), _P]),
     "dms_odom_rgb_step": (C.c_int, [_P, C.c_int, C.c_float, _F3, C.POINTER(C.c_int64), _P]),

@@ -24,20 +24,16 @@ static const int ACC_SLOTS = 192;
 static const int MAX_TRACE = 160;   // >= 3*50 interMap iterations
 
 // Device-resident control block of the persistent tracking kernel.
+static const int SYNC_WORDS = 32 * 17;  // barrier words: arrive counter + 16 release-flag copies, one 128-byte line each
+// Words of Ctrl::pub, the block the solver publishes for the workers' next phase (read once per CTA per barrier).
+enum { PUB_RCURR = 0, PUB_TCURR = 9, PUB_KRKINV = 12, PUB_KT = 21, PUB_SIGMA = 24, PUB_BRK = 25, PUB_SO3DONE = 26,
+       PUB_SO3H = 27, PUB_SO3KINV = 36, PUB_SO3KRLR = 45, PUB_WORDS = 64 };
 struct Ctrl {
-  unsigned int arrive, gen, bad, pad0;
-  double resultRt[16];
-  double resultR[9], lastResultR[9];
-  float Rcurr[9], tcurr[3];
-  float krkinv[9], kt[3];
-  float sigma;
-  int brk, so3_done, n_trace;
-  float icp_vals[28];
-  long long icp_count, rgb_count, rgb_sigma;
-  float R_lr[9], so3_H[9], so3_kinv[9], so3_krlr[9];
-  float so3_lastError, so3_lastCount;
-  float lastRGBError, pad1;
+  float pub[PUB_WORDS];      // 256 bytes = two lines; ints are stored as bit patterns
+  unsigned int bad, pad0;
+  int n_trace, n_dbg;
   unsigned long long t_so3, t_phaseA, t_phaseB, t_mark;  // ns spent per phase kind (Stopwatch keys)
+  unsigned long long t_ser_so3, t_ser_a, t_ser_b, t_start, t_prologue;  // of which: inside the serial sections
   dms_odom_result res;
   float out_R[9], out_t[3];
 };
@@ -49,11 +45,15 @@ struct TrackParams {
   float Rprev[9], tprev[3], Rprev_inv[9];
   float distThres, angleThres;
   int iters[3];
+  double Kd[3][9], Kinv[3][9];  // level intrinsics matrix and its inverse (RO.cpp:415-421, K.inverse())
   Ctrl* ctrl;
+  unsigned int* sync;
   unsigned long long* acc;
   dms_iter_record* trace;
   int timing;
+  unsigned long long* dbg;  // timing mode: CTA 0 logs {tag, globaltimer} pairs here (MAX_DBG pairs)
 };
+static const int MAX_DBG = 1024;
 
 int track_max_grid(int device, int* block_threads);  // co-resident CTAs for the cooperative launch
 cudaError_t launch_track(const TrackParams& p, int grid, cudaStream_t s);

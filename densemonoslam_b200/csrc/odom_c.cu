@@ -21,9 +21,11 @@ struct dms_odom {
   size_t slab_bytes;
   float* zdepth;         // level-0 depth of the last loaded vertex map (stands in for vmaps_tmp, RO.cpp:104,213)
   Ctrl* ctrl;
+  unsigned int* sync;
   unsigned long long* acc;
   dms_iter_record* trace;
   StepOut* step_out;
+  unsigned long long* dbg;
   unsigned char* mask;   // level-0 sized scratch for dms_odom_icp_step's inlier mask
   // staging for the *_host entry points (allocated on first use)
   float4 *stage_v4, *stage_n4; uchar4* stage_rgba; unsigned short* stage_depth;
@@ -165,9 +167,11 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   }
   want((void**)&h->zdepth, (size_t)h->lv[0].rows * h->lv[0].pitch_f32);
   want((void**)&h->ctrl, sizeof(Ctrl));
+  want((void**)&h->sync, sizeof(unsigned int) * SYNC_WORDS);
   want((void**)&h->acc, (size_t)ACC_SLOTS * ACC_STRIDE * sizeof(unsigned long long));
   want((void**)&h->trace, sizeof(dms_iter_record) * MAX_TRACE);
   want((void**)&h->step_out, sizeof(StepOut));
+  want((void**)&h->dbg, sizeof(unsigned long long) * 2 * MAX_DBG);
   want((void**)&h->mask, (size_t)h->lv[0].rows * h->lv[0].pitch_u8);
   for (int r = 0; r < nreq; ++r) off += align_up(reqs[r].bytes, 256);
   h->slab_bytes = off;
@@ -192,6 +196,10 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   int tpb = 0;
   h->grid = track_max_grid(device, &tpb);
   if (h->grid <= 0) { dms_odom_destroy(h); return DMS_ERR_DEVICE; }
+  if (const char* g = getenv("DMS_TRACK_GRID")) {  // tuning knob: fewer co-resident CTAs than the maximum
+    const int v = atoi(g);
+    if (v > 0 && v < h->grid) h->grid = v;
+  }
   *out = h;
   return DMS_OK;
 }
@@ -338,7 +346,15 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   P.iters[0] = interMap ? 50 : fastOdom ? 3 : 10;  // RO.cpp:387-389
   P.iters[1] = interMap ? 50 : pyramid ? 5 : 0;
   P.iters[2] = interMap ? 50 : pyramid ? 4 : 0;
-  P.ctrl = h->ctrl; P.acc = h->acc; P.trace = h->trace; P.timing = h->timing;
+  for (int i = 0; i < 3; ++i) {
+    const Intr& k = h->lv[i].intr;
+    const double Kd[9] = {k.fx, 0, k.cx, 0, k.fy, k.cy, 0, 0, 1};
+    double Ki[9];
+    mat3_inv_host<double>(Kd, Ki);
+    memcpy(P.Kd[i], Kd, sizeof Kd); memcpy(P.Kinv[i], Ki, sizeof Ki);
+  }
+  P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->trace; P.timing = h->timing;
+  P.dbg = h->timing ? h->dbg : nullptr;
   if (h->timing) CK(cudaEventRecord(h->ev0, s));
   cudaError_t e = launch_track(P, h->grid, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
@@ -359,6 +375,7 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
     h->h_ctrl->res = h->last;
     cudaMemcpy(h->ctrl, h->h_ctrl, sizeof(Ctrl), cudaMemcpyHostToDevice);
     cudaMemset(h->acc, 0, (size_t)ACC_SLOTS * ACC_STRIDE * sizeof(unsigned long long));
+    cudaMemset(h->sync, 0, sizeof(unsigned int) * SYNC_WORDS);
     return fail(h, (int)e, "k_track");
   }
   const Ctrl* C = h->h_ctrl;
@@ -372,6 +389,10 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
     h->last_timing.icpStep_ms = (float)(C->t_phaseA * 1e-6);  // ICP rows + photometric residual are one fused pass
     h->last_timing.computeRgbResidual_ms = 0.f;
     h->last_timing.rgbStep_ms = (float)(C->t_phaseB * 1e-6);
+    h->last_timing.prologue_ms = (float)(C->t_prologue * 1e-6);
+    h->last_timing.serial_so3_ms = (float)(C->t_ser_so3 * 1e-6);
+    h->last_timing.serial_a_ms = (float)(C->t_ser_a * 1e-6);
+    h->last_timing.serial_b_ms = (float)(C->t_ser_b * 1e-6);
   }
   return DMS_OK;
 }
@@ -391,6 +412,17 @@ int dms_odom_get_trace(dms_odom* h, dms_iter_record* recs, int max_records, int*
   if (n > max_records) n = max_records;
   if (n > 0 && recs) CK(cudaMemcpy(recs, h->trace, sizeof(dms_iter_record) * n, cudaMemcpyDeviceToHost));
   *n_records = n;
+  return DMS_OK;
+}
+
+int dms_odom_get_timeline(dms_odom* h, uint64_t* pairs, int max_pairs, int* n_pairs) {
+  if (!h || !n_pairs) return fail(h, DMS_ERR_INVALID, "get_timeline: null argument");
+  Bind b(h->device);
+  int n = h->h_ctrl->n_dbg;
+  if (n > MAX_DBG) n = MAX_DBG;
+  if (n > max_pairs) n = max_pairs;
+  if (n > 0 && pairs) CK(cudaMemcpy(pairs, h->dbg, sizeof(unsigned long long) * 2 * n, cudaMemcpyDeviceToHost));
+  *n_pairs = n;
   return DMS_OK;
 }
 

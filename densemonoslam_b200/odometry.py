@@ -224,6 +224,12 @@ class RGBDOdometry:
                         "R": np.array(r.R[:], np.float32).reshape(3, 3), "t": np.array(r.t[:], np.float32)})
         return out
 
+    def timeline(self):
+        buf = (C.c_uint64 * 2048)()
+        n = C.c_int()
+        self._ck(self._L.dms_odom_get_timeline(self._h, buf, 1024, C.byref(n)), "get_timeline")
+        return [(int(buf[2 * i]), int(buf[2 * i + 1])) for i in range(n.value)]
+
     def set_timing(self, enabled=True):
         self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")
 
@@ -232,7 +238,8 @@ class RGBDOdometry:
         self._ck(self._L.dms_odom_get_timing(self._h, C.byref(t)), "get_timing")
         # the reference's Stopwatch keys (RO.cpp:336,444,495,525)
         return {"track": t.track_ms, "so3Step": t.so3Step_ms, "computeRgbResidual": t.computeRgbResidual_ms,
-                "icpStep": t.icpStep_ms, "rgbStep": t.rgbStep_ms}
+                "icpStep": t.icpStep_ms, "rgbStep": t.rgbStep_ms, "prologue": t.prologue_ms, "serial_so3": t.serial_so3_ms,
+                "serial_a": t.serial_a_ms, "serial_b": t.serial_b_ms}
 
     # ------------------------------------------------------------------ step operators (cudafuncs.cuh free functions)
     def icpStep(self, level, Rcurr, tcurr, Rprev_inv, tprev, want_mask=False, stream=None):

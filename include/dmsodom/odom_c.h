@@ -56,7 +56,10 @@ typedef struct dms_odom_result {
  * timing is enabled with dms_odom_set_timing(); milliseconds of the last track call. */
 typedef struct dms_odom_timing {
   float track_ms;   /* whole getIncrementalTransformation on the device */
-  float so3Step_ms, computeRgbResidual_ms, icpStep_ms, rgbStep_ms; /* estimated split by phase cycle counters */
+  float so3Step_ms, computeRgbResidual_ms, icpStep_ms, rgbStep_ms; /* split by the kernel's own phase timers */
+  /* diagnostics: derivative prologue, and the part of each key spent in the single-CTA serial sections
+   * (accumulator read-out, solve, pose update) while the rest of the grid waits */
+  float prologue_ms, serial_so3_ms, serial_a_ms, serial_b_ms;
 } dms_odom_timing;
 
 /* ---- lifetime: RGBDOdometry::RGBDOdometry / ~RGBDOdometry (RO.cpp:21-116).
@@ -141,6 +144,9 @@ typedef struct dms_iter_record {
   float R[9], t[3];
 } dms_iter_record;
 int dms_odom_get_trace(dms_odom* h, dms_iter_record* h_records, int max_records, int* n_records);
+/* Timing mode only: {tag, nanosecond timestamp} pairs logged by CTA 0 of the tracking kernel at its phase
+ * boundaries during the last track call (diagnostic for tools/track_timing.py). */
+int dms_odom_get_timeline(dms_odom* h, uint64_t* h_pairs, int max_pairs, int* n_pairs);
 
 /* ---- single-step operators: the free functions of cudafuncs.cuh that RGBDOdometry (and
  * MutualInformation / KeyFrame / FGROdometry) call.  They act on the handle's pyramid

@@ -31,11 +31,11 @@
 //     measured against oracle/_ref, not gated).
 //   * float -> int pixel rounding = CUDA __float2int_rn (ties to even, NaN -> 0,
 //     saturating).
-//   * reductions: "canonical tree" -- the image is cut into quads (4 consecutive pixels
-//     of a row), a quad is summed sequentially in fp32 (fma accumulation of the row
-//     products), 32 consecutive quads (a segment) are summed sequentially in fp32, and
-//     segment sums are accumulated EXACTLY in a 2x64-bit fixed-point accumulator, so
-//     the result does not depend on how segments are scheduled.  Counts are integers.
+//   * reductions: "canonical tree" -- every image row is cut into segments of 32
+//     consecutive pixels; a pixel's products row[i]*row[j] are fp32 multiplies, the 32
+//     pixels of a segment are added sequentially (pixel 0 first) in fp32, and segment
+//     sums are accumulated EXACTLY in a 2x64-bit fixed-point accumulator, so the result
+//     does not depend on how segments are scheduled.  Counts are integers.
 // =====================================================================================
 #include <algorithm>
 #include <climits>
@@ -111,18 +111,17 @@ struct Exact {
   }
 };
 
-static const int QUAD = 4;      // pixels per quad
-static const int SEGQ = 32;     // quads per segment
+static const int SEGW = 32;     // pixels per segment: 32 consecutive pixels of one image row (one GPU warp)
 
-// Generic canonical reduction.  pix(x, y, row[NR], &flag) fills the Jacobian row of one
-// pixel and returns true when the pixel contributes; products row[i]*row[j] (i<=j) are
-// accumulated, plus the integer count of contributing pixels.
+// Generic canonical reduction.  pix(x, y, row[NR]) fills the Jacobian row of one pixel and returns true
+// when the pixel contributes.  Per pixel the products row[i]*row[j] (i<=j) are formed (fp32 multiply);
+// within a segment they are added sequentially, pixel 0 first (fp32); segment sums are accumulated
+// exactly.  The count of contributing pixels is an integer.
 template <int NR, class PixFn>
 static void canonical_products(int rows, int cols, PixFn pix, float* out_products, int64_t* out_count) {
   const int NP = NR * (NR + 1) / 2;
-  const int qpr = (cols + QUAD - 1) / QUAD;
-  const long nq = (long)rows * qpr;
-  const long nseg = (nq + SEGQ - 1) / SEGQ;
+  const int spr = (cols + SEGW - 1) / SEGW;
+  const long nseg = (long)rows * spr;
   Exact total[NP];
   int64_t count = 0;
 #pragma omp parallel
@@ -131,28 +130,19 @@ static void canonical_products(int rows, int cols, PixFn pix, float* out_product
     int64_t lcount = 0;
 #pragma omp for schedule(static)
     for (long s = 0; s < nseg; ++s) {
+      const int y = (int)(s / spr);
+      const int x0 = (int)(s - (long)y * spr) * SEGW;
       float segacc[NP];
       for (int k = 0; k < NP; ++k) segacc[k] = 0.0f;
-      for (int ql = 0; ql < SEGQ; ++ql) {
-        const long q = s * SEGQ + ql;
-        float qacc[NP];
-        for (int k = 0; k < NP; ++k) qacc[k] = 0.0f;
-        if (q < nq) {
-          const int y = (int)(q / qpr);
-          const int x0 = (int)(q - (long)y * qpr) * QUAD;
-          for (int p = 0; p < QUAD; ++p) {
-            const int x = x0 + p;
-            if (x >= cols) break;
-            float row[NR];
-            if (pix(x, y, row)) {
-              ++lcount;
-              int k = 0;
-              for (int i = 0; i < NR; ++i)
-                for (int j = i; j < NR; ++j, ++k) qacc[k] = fmaf(row[i], row[j], qacc[k]);
-            }
-          }
+      for (int l = 0; l < SEGW; ++l) {
+        const int x = x0 + l;
+        float row[NR];
+        if (x < cols && pix(x, y, row)) {
+          ++lcount;
+          int k = 0;
+          for (int i = 0; i < NR; ++i)
+            for (int j = i; j < NR; ++j, ++k) segacc[k] = segacc[k] + row[i] * row[j];
         }
-        for (int k = 0; k < NP; ++k) segacc[k] = segacc[k] + qacc[k];
       }
       for (int k = 0; k < NP; ++k) loc[k].addf(segacc[k]);
     }
@@ -585,6 +575,47 @@ static void unpack_so3(const float p[10], float A[9], float b[3]) {  // reduce.c
     }
 }
 
+// Reciprocal used by the fp64 solver steps: IEEE fp32 division as the seed, two Newton steps in fp64 with
+// explicit fma.  Accurate to ~1 ulp of fp64 and, unlike a hardware reciprocal, identical on CPU and GPU
+// (a correctly rounded fp64 division costs ~400 cycles on the one GPU warp every iteration waits for).
+static inline double rcp_nr(double d) {
+  double r = (double)(1.0f / (float)d);
+  r = fma(r, fma(-d, r, 1.0), r);
+  r = fma(r, fma(-d, r, 1.0), r);
+  return r;
+}
+static inline float rcp_nr(float d) { return 1.0f / d; }  // the 3x3 fp32 system keeps IEEE division
+
+// sin / cos for Rodrigues.  Below 0.25 rad (every realistic Gauss-Newton update) an explicit Taylor
+// polynomial in plain fp64 mul/add: truncation < 2e-25, and bit-identical on CPU and GPU.  Larger angles
+// fall back to the platform's sincos (libm / libdevice agree to ~1 ulp).
+static inline void sincos_small(double t, double* sn, double* cs) {
+  if (t < 0.25) {
+    const double t2 = t * t;
+    double s = -7.6471637318198164759e-13;                       // -1/15!
+    s = s * t2 + 1.6059043836821614599e-10;                      //  1/13!
+    s = s * t2 + -2.5052108385441718775e-08;                     // -1/11!
+    s = s * t2 + 2.7557319223985890653e-06;                      //  1/9!
+    s = s * t2 + -1.9841269841269841270e-04;                     // -1/7!
+    s = s * t2 + 8.3333333333333333333e-03;                      //  1/5!
+    s = s * t2 + -1.6666666666666666667e-01;                     // -1/3!
+    s = s * t2 + 1.0;
+    *sn = t * s;
+    double c = 4.7794773323873852974e-14;                        //  1/16!
+    c = c * t2 + -1.1470745597729724714e-11;                     // -1/14!
+    c = c * t2 + 2.0876756987868098979e-09;                      //  1/12!
+    c = c * t2 + -2.7557319223985890653e-07;                     // -1/10!
+    c = c * t2 + 2.4801587301587301587e-05;                      //  1/8!
+    c = c * t2 + -1.3888888888888888889e-03;                     // -1/6!
+    c = c * t2 + 4.1666666666666666667e-02;                      //  1/4!
+    c = c * t2 + -0.5;
+    c = c * t2 + 1.0;
+    *cs = c;
+  } else {
+    *sn = sin(t); *cs = cos(t);
+  }
+}
+
 // LDL^T solve without pivoting (stands in for Eigen ldlt().solve, RO.cpp:554-566,371).
 // One reciprocal per pivot, then multiplications (the device solver does the same).
 template <class T, int N>
@@ -595,7 +626,7 @@ static void ldlt_solve(const T* A, const T* b, T* x) {
     T d = A[j * N + j];
     for (int k = 0; k < j; ++k) d = d - (L[j * N + k] * L[j * N + k]) * D[k];
     D[j] = d;
-    iD[j] = T(1) / d;
+    iD[j] = rcp_nr(d);
     for (int i = j + 1; i < N; ++i) {
       T s = A[i * N + j];
       for (int k = 0; k < j; ++k) s = s - (L[i * N + k] * L[j * N + k]) * D[k];
@@ -610,7 +641,7 @@ static void ldlt_solve(const T* A, const T* b, T* x) {
   for (int i = 0; i < N; ++i) y[i] = y[i] * iD[i];
   for (int i = N - 1; i >= 0; --i) {
     T s = y[i];
-    for (int k = i + 1; k < N; ++k) s = s - L[k * N + i] * x[k];
+    for (int k = N - 1; k > i; --k) s = s - L[k * N + i] * x[k];  // last unknown first (right-looking order)
     x[i] = s;
   }
 }
@@ -630,14 +661,26 @@ static void mat3_inv(const T* m, T* o) {
   o[6] = c02 * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
 }
 
+// same cofactor inverse with the Newton reciprocal (device-side use: Rt^-1 of RO.cpp:427)
+static void mat3_inv_nr(const double* m, double* o) {
+  const double c00 = m[4] * m[8] - m[5] * m[7], c01 = m[5] * m[6] - m[3] * m[8], c02 = m[3] * m[7] - m[4] * m[6];
+  const double det = m[0] * c00 + m[1] * c01 + m[2] * c02;
+  const double id = rcp_nr(det);
+  o[0] = c00 * id; o[1] = (m[2] * m[7] - m[1] * m[8]) * id; o[2] = (m[1] * m[5] - m[2] * m[4]) * id;
+  o[3] = c01 * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[2] * m[3] - m[0] * m[5]) * id;
+  o[6] = c02 * id; o[7] = (m[1] * m[6] - m[0] * m[7]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
+}
+
 // OP.h:35-71 rodrigues
 static void rodrigues(const double r[3], double R[9]) {
   double rx = r[0], ry = r[1], rz = r[2];
   const double theta = sqrt(rx * rx + ry * ry + rz * rz);
   const double I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   if (theta >= 2.2204460492503131e-16) {
-    const double c = cos(theta), s = sin(theta), c1 = 1. - c;
-    const double itheta = theta ? 1. / theta : 0.;
+    double s, c;
+    sincos_small(theta, &s, &c);
+    const double c1 = 1. - c;
+    const double itheta = theta ? rcp_nr(theta) : 0.;
     rx *= itheta; ry *= itheta; rz *= itheta;
     const double rrt[9] = {rx * rx, rx * ry, rx * rz, rx * ry, ry * ry, ry * rz, rx * rz, ry * rz, rz * rz};
     const double rx_[9] = {0, -rz, ry, rz, 0, -rx, -ry, rx, 0};
@@ -823,7 +866,7 @@ struct Odom {
         // Rt = resultRt.inverse(): affine [R t; 0 1] -> [R^-1, -R^-1 t]
         double R3[9], Ri[9], ti[3];
         for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) R3[r * 3 + c] = resultRt[r * 4 + c];
-        mat3_inv(R3, Ri);
+        mat3_inv_nr(R3, Ri);
         for (int r = 0; r < 3; ++r) ti[r] = -(Ri[r * 3 + 0] * resultRt[3] + Ri[r * 3 + 1] * resultRt[7] + Ri[r * 3 + 2] * resultRt[11]);
         double KR[9], KRKi[9]; mat3_mul(Kd, Ri, KR); mat3_mul(KR, Kinv, KRKi);
         const M33 krkInv = m33_from(KRKi);

@@ -41,12 +41,15 @@ def test_library_has_sm100a_code_and_no_oracle_dependency():
 
 
 def test_product_package_never_imports_oracle():
+    """The product may mention the oracle in comments, but must not include, import, link or load it."""
     pkg = os.path.join(ROOT, "densemonoslam_b200")
+    forbidden = ("oracle/", "import oracle", "from oracle", "liboracle", "cpu_odom", "oracle.oracle", "_ref/")
     for dp, _, fs in os.walk(pkg):
         for f in fs:
-            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".sh")):
                 txt = open(os.path.join(dp, f)).read()
-                assert "oracle" not in txt.replace("CPU oracle", "").replace("the oracle", "").replace("oracle's", ""), os.path.join(dp, f)
+                for pat in forbidden:
+                    assert pat not in txt, (os.path.join(dp, f), pat)
 
 
 def test_create_fails_loudly_without_gpu():
