@@ -64,6 +64,7 @@ SIGNATURES = {
     "dms_odom_get_buffer": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(_P), C.POINTER(C.c_size_t), C.POINTER(C.c_int),
                                       C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "dms_odom_download": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_size_t, _P]),
+    "dms_odom_set_trace": (C.c_int, [_P, C.c_int]),
     "dms_odom_get_trace": (C.c_int, [_P, C.POINTER(DmsIterRecord), C.c_int, C.POINTER(C.c_int)]),
     "dms_odom_get_timeline": (C.c_int, [_P, C.POINTER(C.c_uint64), C.c_int, C.POINTER(C.c_int)]),
     "dms_odom_icp_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P, _P]),

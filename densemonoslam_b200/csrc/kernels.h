@@ -43,7 +43,7 @@ struct TrackParams {
   int rgbOnly, pyramid, fastOdom, so3, interMap, icp, rgb;
   float icpWeight;
   float Rprev[9], tprev[3], Rprev_inv[9];
-  float distThres, angleThres;
+  float dist2Max, sine2Lim;  // squared-domain equivalents of distThres / angleThres (threshold_equiv)
   int iters[3];
   double Kd[3][9], Kinv[3][9];  // level intrinsics matrix and its inverse (RO.cpp:415-421, K.inverse())
   Ctrl* ctrl;
@@ -55,6 +55,7 @@ struct TrackParams {
 };
 static const int MAX_DBG = 1024;
 
+void threshold_equiv(float distThres, float angleThres, float* dist2Max, float* sine2Lim);
 int track_max_grid(int device, int* block_threads);  // co-resident CTAs for the cooperative launch
 cudaError_t launch_track(const TrackParams& p, int grid, cudaStream_t s);
 

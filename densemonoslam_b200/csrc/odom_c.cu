@@ -32,7 +32,7 @@ struct dms_odom {
   // pinned host mirror of Ctrl / StepOut
   Ctrl* h_ctrl; StepOut* h_step;
   int grid;              // co-resident CTAs of the cooperative tracking kernel
-  int timing;
+  int timing, tracing;
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
   cudaEvent_t ev0, ev1;
@@ -130,7 +130,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   h->K.fx = fx; h->K.fy = fy; h->K.cx = cx; h->K.cy = cy;
   h->distThres = distThresh; h->angleThres = angleThresh;
   h->slab = nullptr; h->stage_v4 = h->stage_n4 = nullptr; h->stage_rgba = nullptr; h->stage_depth = nullptr;
-  h->h_ctrl = nullptr; h->h_step = nullptr; h->timing = 0; h->ev0 = h->ev1 = nullptr;
+  h->h_ctrl = nullptr; h->h_step = nullptr; h->timing = 0; h->tracing = 0; h->ev0 = h->ev1 = nullptr;
   memset(&h->last, 0, sizeof h->last); memset(&h->last_timing, 0, sizeof h->last_timing);
   // RO.cpp:26-31 initial public state
   h->last.lastICPCount = h->last.lastRGBCount = h->last.lastSO3Count = (float)(width * height);
@@ -342,7 +342,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   P.icpWeight = icpWeight;
   memcpy(P.Rprev, rot, sizeof P.Rprev); memcpy(P.tprev, trans, sizeof P.tprev);
   mat3_inv_host<float>(P.Rprev, P.Rprev_inv);
-  P.distThres = h->distThres; P.angleThres = h->angleThres;
+  threshold_equiv(h->distThres, h->angleThres, &P.dist2Max, &P.sine2Lim);
   P.iters[0] = interMap ? 50 : fastOdom ? 3 : 10;  // RO.cpp:387-389
   P.iters[1] = interMap ? 50 : pyramid ? 5 : 0;
   P.iters[2] = interMap ? 50 : pyramid ? 4 : 0;
@@ -353,9 +353,9 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
     mat3_inv_host<double>(Kd, Ki);
     memcpy(P.Kd[i], Kd, sizeof Kd); memcpy(P.Kinv[i], Ki, sizeof Ki);
   }
-  P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->trace; P.timing = h->timing;
+  P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = h->timing;
   P.dbg = h->timing ? h->dbg : nullptr;
-  if (h->timing) CK(cudaEventRecord(h->ev0, s));
+  if (h->timing) { CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s)); CK(cudaEventRecord(h->ev0, s)); }
   cudaError_t e = launch_track(P, h->grid, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
   if (h->timing) CK(cudaEventRecord(h->ev1, s));
@@ -404,10 +404,12 @@ int dms_odom_track(dms_odom* h, float trans[3], float rot[9], int rgbOnly, float
   return dms_odom_track_collect(h, trans, rot, stream, out);
 }
 
+int dms_odom_set_trace(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->tracing = enabled ? 1 : 0; return DMS_OK; }
+
 int dms_odom_get_trace(dms_odom* h, dms_iter_record* recs, int max_records, int* n_records) {
   if (!h || !n_records) return fail(h, DMS_ERR_INVALID, "get_trace: null argument");
   Bind b(h->device);
-  int n = h->h_ctrl->n_trace;
+  int n = h->tracing ? h->h_ctrl->n_trace : 0;
   if (n > MAX_TRACE) n = MAX_TRACE;
   if (n > max_records) n = max_records;
   if (n > 0 && recs) CK(cudaMemcpy(recs, h->trace, sizeof(dms_iter_record) * n, cudaMemcpyDeviceToHost));
@@ -418,8 +420,7 @@ int dms_odom_get_trace(dms_odom* h, dms_iter_record* recs, int max_records, int*
 int dms_odom_get_timeline(dms_odom* h, uint64_t* pairs, int max_pairs, int* n_pairs) {
   if (!h || !n_pairs) return fail(h, DMS_ERR_INVALID, "get_timeline: null argument");
   Bind b(h->device);
-  int n = h->h_ctrl->n_dbg;
-  if (n > MAX_DBG) n = MAX_DBG;
+  int n = MAX_DBG;  // CTA 0 logs from entry 0, the solver from entry 512; unused entries are zero
   if (n > max_pairs) n = max_pairs;
   if (n > 0 && pairs) CK(cudaMemcpy(pairs, h->dbg, sizeof(unsigned long long) * 2 * n, cudaMemcpyDeviceToHost));
   *n_pairs = n;

@@ -212,6 +212,9 @@ class RGBDOdometry:
             return a.reshape(3, rows // 3, cols)
         return a.reshape(rows, cols)
 
+    def set_trace(self, enabled=True):
+        self._ck(self._L.dms_odom_set_trace(self._h, int(enabled)), "set_trace")
+
     def trace(self):
         recs = (_lib.DmsIterRecord * 160)()
         n = C.c_int()
@@ -228,7 +231,7 @@ class RGBDOdometry:
         buf = (C.c_uint64 * 2048)()
         n = C.c_int()
         self._ck(self._L.dms_odom_get_timeline(self._h, buf, 1024, C.byref(n)), "get_timeline")
-        return [(int(buf[2 * i]), int(buf[2 * i + 1])) for i in range(n.value)]
+        return [(int(buf[2 * i]), int(buf[2 * i + 1])) for i in range(n.value) if buf[2 * i + 1]]
 
     def set_timing(self, enabled=True):
         self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")

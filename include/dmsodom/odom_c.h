@@ -134,7 +134,7 @@ int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t*
 /* Copies a buffer to dense host memory (rows*cols*elem_bytes, planar maps 3 planes). */
 int dms_odom_download(dms_odom* h, int which, int level, void* h_dst, size_t dst_bytes, void* stream);
 
-/* Per-iteration trace of the last track call (for parity tests): record i holds
+/* Per-iteration trace of the last track call (for parity tests; enable with dms_odom_set_trace): record i holds
  * {level, iter, icp_inliers, rgb_count, rgb_sigma} and the 28 ICP / 28 RGB reduced values
  * (27 products in JtJJtrSE3 order, types.cuh:117-131, then residual) and the pose after it. */
 typedef struct dms_iter_record {
@@ -143,6 +143,7 @@ typedef struct dms_iter_record {
   float icp[28], rgb[28];
   float R[9], t[3];
 } dms_iter_record;
+int dms_odom_set_trace(dms_odom* h, int enabled); /* off by default: recording costs a little solver time */
 int dms_odom_get_trace(dms_odom* h, dms_iter_record* h_records, int max_records, int* n_records);
 /* Timing mode only: {tag, nanosecond timestamp} pairs logged by CTA 0 of the tracking kernel at its phase
  * boundaries during the last track call (diagnostic for tools/track_timing.py). */

@@ -476,7 +476,9 @@ static inline bool rgb_step_pixel(const RgbStepArgs& a, int x, int y, float row[
   const float z = a.lastDepth[(size_t)c.v0 * a.cols + c.u0];
   const float invFx = 1.0f / a.intr.fx, invFy = 1.0f / a.intr.fy;
   const V3 cp = v3(((float)c.u0 - a.intr.cx) * z * invFx, ((float)c.v0 - a.intr.cy) * z * invFy, z);
-  const float invz = (float)(1.0 / (double)cp.z);
+  // reduce.cu:584 divides in double and rounds to float; a single IEEE fp32 division gives the same float
+  // except on double-rounding ties (probability ~2e-9 per pixel) and is what the kernels use
+  const float invz = 1.0f / cp.z;
   const float dI_dx_val = w * a.sobelScale * (float)a.dIdx[k];
   const float dI_dy_val = w * a.sobelScale * (float)a.dIdy[k];
   const float v0 = dI_dx_val * a.intr.fx * invz;

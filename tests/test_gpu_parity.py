@@ -30,6 +30,7 @@ def make_pair(synth, cam, seed=1234, **kw):
 def both(orc, synth, cam, distThresh=0.10):
     from densemonoslam_b200.odometry import RGBDOdometry, DEFAULT_ANGLE_THRESH
     g = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, distThresh, DEFAULT_ANGLE_THRESH)
+    g.set_trace(True)
     o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, distThresh, DEFAULT_ANGLE_THRESH)
     return g, o
 
@@ -290,6 +291,7 @@ def test_large_frame_properties_1080p(torch_cuda, orc, synth):
     model, live, T = synth.frame_pair(cam, seed=99)
     from densemonoslam_b200.odometry import RGBDOdometry
     g = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    g.set_trace(True)
     pose = np.eye(4, dtype=np.float32)
     cv = lambda a: to_dev(torch_cuda, a)
     runs = []

@@ -25,7 +25,15 @@ for i in range(N + 5):
             acc[k] = acc.get(k, 0.0) + v / N
 print(name, json.dumps({k: round(v * 1000, 1) for k, v in acc.items()}), "us; iters", g.iters, "so3", g.so3_iters)
 
-tl = g.timeline()
+tl_all = g.timeline()
+tl = [e for e in tl_all if e[0] < 200]
+stl = [e for e in tl_all if e[0] >= 200]
+sagg = {}
+for (a, ta), (b, tb) in zip(stl[:-1], stl[1:]):
+    if b > a:
+        v = sagg.setdefault(f"solver {a}->{b}", [0, 0.0]); v[0] += 1; v[1] += (tb - ta) / 1000.0
+for k, (n, tot) in sagg.items():
+    print(f"  {k:30s} n={n:3d} mean={tot / n:6.2f} us")
 t0 = tl[0][1]
 names = {10: "so3 start", 11: "so3 loop done (warp0)", 12: "so3 arrived", 13: "so3 barrier exit", 20: "A start L0", 21: "A start L1", 22: "A start L2",
          30: "A loop done (warp0)", 31: "A arrived", 32: "A barrier exit", 40: "B loop done (warp0)", 41: "B arrived", 42: "B barrier exit", 99: "end"}
