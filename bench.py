@@ -143,6 +143,37 @@ def run_oracle_frames(cam, frames, n_frames, budget_s, threads=None):
     return done, time.perf_counter() - t0, orc.num_threads()
 
 
+def run_legacy_frames(cam, frames, n_frames, budget_s):
+    """Reported baseline: the reference's own legacy kernels (oracle/_ref, built unmodified from /root/reference for
+    sm_100a) driven by the reference's host loop (blocking sync + download after every kernel), inputs resident on the device."""
+    try:
+        from oracle import ref_legacy
+        if not ref_legacy.available():
+            return None
+        r = ref_legacy.LegacyOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+        n = min(len(frames), 8)
+        for i in range(n):
+            f = frames[i]
+            r.upload(2 * i, v4=f["model"]["vmap4"], n4=f["model"]["nmap4"], rgba=f["model"]["rgba"])
+            r.upload(2 * i + 1, rgba=f["live"]["rgba"], depth=f["live"]["depth"])
+        r.initFirstRGB(1)
+
+        def one(i):
+            f = frames[i % n]; p = f["prior"]; a, b = 2 * (i % n), 2 * (i % n) + 1
+            r.initICPModel(a, p); r.initRGBModel(a); r.initICP(b, 25.0); r.initRGB(b)
+            return r.getIncrementalTransformation(p[:3, 3].copy(), p[:3, :3].copy(), FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"], FLAGS["so3"])
+        for i in range(3):
+            one(i)
+        done, t0 = 0, time.perf_counter()
+        while done < n_frames and time.perf_counter() - t0 < budget_s:
+            one(done); done += 1
+        secs = time.perf_counter() - t0
+        return {"value": done / secs, "unit": "frames/s", "ms_per_frame": 1000.0 * secs / done, "sample": f"{done} frames",
+                "note": "reference's own reduce.cu / cudafuncs.cu compiled for sm_100a + the reference's host loop (sync and D2H after every kernel); reported baseline, not the target"}
+    except Exception as e:  # a baseline must never break the bench line
+        return {"unavailable": repr(e)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -302,6 +333,10 @@ def main():
                                "sample": f"{done} frames of the same workload in {secs:.1f} s (OpenMP oracle, all host threads)"}
         done1, secs1, _ = run_oracle_frames(cam, host_frames, 40, 6.0, threads=1)
         out["cpu_baseline"]["single_thread_value"] = done1 / secs1
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        legacy = run_legacy_frames(cam, frames, 200, 10.0)
+        if legacy:
+            out["legacy_cuda"] = legacy
     if rank == 0:
         print(json.dumps(out))
     if world > 1:

@@ -111,3 +111,46 @@ def so3_step(lastImage, nextImage, H_, kinv, krlr, threads=160, blocks=64):
     lib().ref_so3_step(_p(np.ascontiguousarray(lastImage)), _p(np.ascontiguousarray(nextImage)), _p(_f(H_, 9)), _p(_f(kinv, 9)), _p(_f(krlr, 9)),
                        H, W, threads, blocks, _p(A), _p(b), _p(res))
     return A.reshape(3, 3), b, float(res[0]), int(res[1])
+
+
+class LegacyOdometry:
+    """The reference's host loop (RGBDOdometry.cpp:118-605) over the reference's own kernels; inputs are staged
+    on the device in numbered slots first (the reference receives them as GL textures)."""
+
+    def __init__(self, width, height, cx, cy, fx, fy, distThresh=0.10, angleThresh=float(np.sin(np.float32(20.0) * np.float32(3.14159254) / np.float32(180.0)))):
+        L = lib()
+        L.ref_odom_create.restype = C.c_void_p
+        L.ref_odom_create.argtypes = [C.c_int, C.c_int] + [C.c_float] * 6
+        self._h = C.c_void_p(L.ref_odom_create(width, height, cx, cy, fx, fy, distThresh, angleThresh))
+        self.out = np.zeros(6, np.float32)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ref_odom_destroy(self._h); self._h = None
+
+    def upload(self, slot, v4=None, n4=None, rgba=None, depth=None):
+        g = lambda a, dt: None if a is None else _p(np.ascontiguousarray(a, dt))
+        lib().ref_odom_upload(self._h, slot, g(v4, np.float32), g(n4, np.float32), g(rgba, np.uint8), g(depth, np.uint16))
+
+    def initICP(self, slot, cutoff=25.0):
+        lib().ref_odom_init_icp_depth(self._h, slot, C.c_float(cutoff))
+
+    def initICPMaps(self, slot):
+        lib().ref_odom_init_icp_maps(self._h, slot)
+
+    def initICPModel(self, slot, pose):
+        lib().ref_odom_init_icp_model(self._h, slot, _p(_f(pose, 16)))
+
+    def initRGB(self, slot):
+        lib().ref_odom_init_rgb(self._h, slot)
+
+    def initRGBModel(self, slot):
+        lib().ref_odom_init_rgb_model(self._h, slot)
+
+    def initFirstRGB(self, slot):
+        lib().ref_odom_init_first_rgb(self._h, slot)
+
+    def getIncrementalTransformation(self, trans, rot, rgbOnly, icpWeight, pyramid, fastOdom, so3, interMap=False):
+        t = _f(trans, 3).copy(); R = _f(rot, 9).copy()
+        lib().ref_odom_track(self._h, _p(t), _p(R), int(rgbOnly), C.c_float(icpWeight), int(pyramid), int(fastOdom), int(so3), int(interMap), _p(self.out))
+        return t, R.reshape(3, 3)

@@ -43,3 +43,31 @@ def test_intensity_all_colours_match_reference(orc, ref):
     v = np.arange(1 << 24, dtype=np.uint32)
     rgba = np.stack([v & 255, (v >> 8) & 255, (v >> 16) & 255, np.full_like(v, 255)], axis=-1).astype(np.uint8).reshape(4096, 4096, 4)
     assert np.array_equal(orc.bgr_to_intensity(rgba), ref.bgr_to_intensity(rgba))
+
+
+def test_full_track_against_reference_loop(orc, synth, ref):
+    """Whole getIncrementalTransformation: the reference's host loop over its own kernels vs the oracle.
+    The legacy build's fast-math flips a few threshold pixels per iteration, so poses agree to ~1e-4, not bit-exactly."""
+    cam = synth.CAM_VGA
+    model, live, T = synth.frame_pair(cam, seed=1234)
+    pose = np.eye(4, dtype=np.float32)
+    o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    r = ref.LegacyOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    r.upload(0, v4=model["vmap4"], n4=model["nmap4"], rgba=model["rgba"])
+    r.upload(1, rgba=live["rgba"], depth=live["depth"])
+    o.initFirstRGB(model["rgba"]); r.initFirstRGB(0)
+    o.initICPModel(model["vmap4"], model["nmap4"], pose); r.initICPModel(0, pose)
+    o.initRGBModel(model["rgba"]); r.initRGBModel(0)
+    o.initICP(live["depth"], 25.0); r.initICP(1, 25.0)
+    o.initRGB(live["rgba"]); r.initRGB(1)
+    flags = (False, 10.0, True, False, True, False)
+    to, Ro, res = o.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *flags)
+    tr, Rr = r.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *flags)
+    rep = {"t_oracle": to.tolist(), "t_reference": tr.tolist(), "max_dt": float(np.max(np.abs(to - tr))), "max_dR": float(np.max(np.abs(Ro - Rr))),
+           "icp_count": [res.lastICPCount, float(r.out[1])], "rgb_count": [res.lastRGBCount, float(r.out[3])], "so3_count": [res.lastSO3Count, float(r.out[5])],
+           "icp_error": [res.lastICPError, float(r.out[0])], "rgb_error": [res.lastRGBError, float(r.out[2])]}
+    json.dump(rep, open(os.path.join(ROOT, "gpurun_out", "legacy_track_vga.json"), "w"), indent=1)
+    assert rep["max_dt"] < 2e-4 and rep["max_dR"] < 2e-4, rep
+    assert abs(res.lastICPCount - r.out[1]) <= 2e-3 * r.out[1], rep
+    assert abs(res.lastRGBCount - r.out[3]) <= 5e-3 * max(r.out[3], 1), rep
+    assert np.max(np.abs(tr - T[:3, 3])) < 5e-3
