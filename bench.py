@@ -34,6 +34,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLAGS = dict(rgbOnly=False, icpWeight=10.0, pyramid=True, fastOdom=False, so3=True)
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch at 1241x376 (ncu --set full, profiles/): the working
+# set is L2-resident, so DRAM traffic is far BELOW the algorithmic bytes
+TRAFFIC_NCU = 35.7e6
 
 
 def workload_def(name):
@@ -182,6 +185,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
+    ap.add_argument("--pipeline", type=int, default=3, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -238,30 +242,34 @@ def main():
     config["ring_frames"] = ring
     config["cache"] = f"inputs cycle through {ring} distinct resident frames = {ring * per_frame_in / 1e6:.0f} MB (> 126 MB L2)"
 
-    odo = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
-    odo.set_timing(True)
-    stream = torch.cuda.current_stream()
-    odo.initFirstRGB(dev[0]["li"], stream=stream)
+    props = torch.cuda.get_device_properties(local_rank)
+    sms = props.multi_processor_count
 
-    def step_device(i):
-        f, d = frames[i % ring], dev[i % ring]
-        p = f["prior"]
-        odo.initICPModel(d["v"], d["n"], 25.0, p, stream=stream)
-        odo.initRGBModel(d["mi"], stream=stream)
-        odo.initICP(d["d"], 25.0, stream=stream)
-        odo.initRGB(d["li"], stream=stream)
-        return odo.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
-                                                FLAGS["so3"], stream=stream)
+    def make_pipe(depth):
+        """`depth` trackers sharing the GPU (SMs split evenly), each on its own stream.  Frame f goes to tracker
+        f % depth; before it, the tracker's SO(3) reference image is (re)loaded from frame f-1 (initFirstRGB), so the
+        results are those of the sequential single-tracker run."""
+        hs, ss = [], []
+        for k in range(depth):
+            h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
+            h.set_grid(0 if depth == 1 else sms // depth)
+            h.set_timing(True)
+            hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
+        return hs, ss
 
-    def step_host(i):
-        f, h = frames[i % ring], pinned[i % ring]
+    def one_frame(h, st, i, host):
+        f = frames[i % ring]
+        src = pinned if host else dev
+        cur, prev = src[i % ring], src[(i - 1) % ring]
+        get = (lambda t: t.numpy()) if host else (lambda t: t)
         p = f["prior"]
-        odo.initICPModel(h["v"].numpy(), h["n"].numpy(), 25.0, p, stream=stream)
-        odo.initRGBModel(h["mi"].numpy(), stream=stream)
-        odo.initICP(h["d"].numpy(), 25.0, stream=stream)
-        odo.initRGB(h["li"].numpy(), stream=stream)
-        return odo.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
-                                                FLAGS["so3"], stream=stream)
+        h.initFirstRGB(get(prev["li"]), stream=st)
+        h.initICPModel(get(cur["v"]), get(cur["n"]), 25.0, p, stream=st)
+        h.initRGBModel(get(cur["mi"]), stream=st)
+        h.initICP(get(cur["d"]), 25.0, stream=st)
+        h.initRGB(get(cur["li"]), stream=st)
+        return h.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
+                                              FLAGS["so3"], stream=st)
 
     def barrier():
         torch.cuda.synchronize()
@@ -269,21 +277,32 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(step_fn, steps, warmup, collect_kernel_times):
-        for i in range(max(3, warmup)):
-            step_fn(i)
+    def timed(pipe, steps, warmup, host):
+        hs, ss = pipe
+        depth = len(hs)
+        for i in range(max(3, warmup) * depth):
+            one_frame(hs[i % depth], ss[i % depth], i, host)
         barrier()
         sampler = ClockSampler(local_rank)
         sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ktimes, iters_seen, so3_seen = [], [], []
-        ev0.record(stream)
-        for i in range(steps):
-            step_fn(i)
-            if collect_kernel_times:
-                ktimes.append(odo.timing()["track"])
-                iters_seen.append(list(odo.iters)); so3_seen.append(odo.so3_iters)
-        ev1.record(stream)
+        stats = [{"k": [], "it": [], "so3": [], "last": None} for _ in range(depth)]
+
+        def work(k):
+            torch.cuda.set_device(local_rank)
+            for i in range(k, steps, depth):
+                out = one_frame(hs[k], ss[k], i, host)
+                stats[k]["k"].append(hs[k].timing()["track"]); stats[k]["it"].append(list(hs[k].iters)); stats[k]["so3"].append(hs[k].so3_iters)
+                if i == steps - 1:
+                    stats[k]["last"] = out
+        ev0.record()
+        if depth == 1:
+            work(0)
+        else:
+            ths = [threading.Thread(target=work, args=(k,)) for k in range(depth)]
+            [t.start() for t in ths]; [t.join() for t in ths]
+        torch.cuda.synchronize()
+        ev1.record()
         barrier()
         ms = ev0.elapsed_time(ev1)
         clocks = sampler.result()
@@ -291,39 +310,59 @@ def main():
             t = torch.tensor([ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        return ms, ktimes, iters_seen, so3_seen, clocks
+        ktimes = [x for s_ in stats for x in s_["k"]]
+        iters_seen = [x for s_ in stats for x in s_["it"]]
+        so3_seen = [x for s_ in stats for x in s_["so3"]]
+        last = [s_["last"] for s_ in stats if s_["last"] is not None][0]
+        return ms, ktimes, iters_seen, so3_seen, clocks, last
 
-    ms, ktimes, iters_seen, so3_seen, clocks = timed(step_device, args.steps, args.warmup, True)
-    value = world * args.steps / (ms * 1e-3)
-    t_last, R_last = step_device(args.steps - 1)
-    gt = frames[(args.steps - 1) % ring]["gt"]
-    pose_err = float(np.max(np.abs(t_last - gt[:3, 3])))
-
-    e2e_steps = min(args.steps, 300)
-    ms_e2e, _, _, _, _ = timed(step_host, e2e_steps, min(args.warmup, 5), False)
-    e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
-
-    # roofline of the dominant kernel (k_track)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak = float(json.load(open(peaks_path))["hbm_gbs"]); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak = 6650.0; peak_src = "fallback (B200_PROFILING.md)"
-    k_ms = float(np.mean(ktimes))
-    alg = float(np.mean([algorithmic_bytes(cam, it, s3) for it, s3 in zip(iters_seen, so3_seen)]))
-    achieved = alg / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_track (persistent cooperative: derivatives + SO3 + 3-level GN incl. solves)", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg, "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (ms / args.steps),
+
+    def roofline_of(ms, steps, ktimes, iters_seen, so3_seen, depth):
+        k_ms = float(np.mean(ktimes))
+        alg = float(np.mean([algorithmic_bytes(cam, it, s3) for it, s3 in zip(iters_seen, so3_seen)]))
+        # `depth` tracking kernels run concurrently, each on 1/depth of the SMs: the aggregate rate is depth launches per k_ms
+        achieved = depth * alg / (k_ms * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": "k_track (persistent cooperative: derivatives + SO3 + 3-level GN incl. solves)", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg, "kernel_ms": k_ms, "concurrent_launches": depth,
+                "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
+
+    depth = max(1, args.pipeline)
+    config["pipeline"] = (f"{depth} trackers share the GPU ({sms // depth} SMs each, own stream); frame f runs on tracker f % {depth}"
+                          if depth > 1 else "single tracker, frames strictly one after another")
+    pipe = make_pipe(depth)
+    ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
+    value = world * args.steps / (ms * 1e-3)
+    gt = frames[(args.steps - 1) % ring]["gt"]
+    pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
+    roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, depth)
+
+    e2e_steps = min(args.steps, 300)
+    ms_e2e, _, _, _, _, _ = timed(pipe, e2e_steps, min(args.warmup, 5), True)
+    e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
 
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": config, "roofline": roofline,
-           "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in, "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
+           "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + frames[0]["live"]["rgba"].nbytes,
+                   "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
-           "gpu_launches": 11 * args.steps, "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
+           "gpu_launches": 14 * args.steps, "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
            "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
+    if depth > 1 and world == 1:
+        # the same sequence on one tracker owning the whole GPU: per-frame latency and the full-GPU kernel roofline
+        del pipe
+        pipe1 = make_pipe(1)
+        ms1, k1, it1, s31, _, _ = timed(pipe1, min(args.steps, 300), args.warmup, False)
+        n1 = min(args.steps, 300)
+        out["single_tracker"] = {"value": n1 / (ms1 * 1e-3), "unit": "frames/s", "latency_ms_per_frame": ms1 / n1,
+                                 "roofline": roofline_of(ms1, n1, k1, it1, s31, 1)}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         host_frames = frames[: min(ring, 4)]

@@ -31,7 +31,7 @@ struct dms_odom {
   float4 *stage_v4, *stage_n4; uchar4* stage_rgba; unsigned short* stage_depth;
   // pinned host mirror of Ctrl / StepOut
   Ctrl* h_ctrl; StepOut* h_step;
-  int grid;              // co-resident CTAs of the cooperative tracking kernel
+  int grid, grid_max;    // CTAs of the cooperative tracking kernel in use / co-resident maximum
   int timing, tracing;
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
@@ -196,6 +196,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   int tpb = 0;
   h->grid = track_max_grid(device, &tpb);
   if (h->grid <= 0) { dms_odom_destroy(h); return DMS_ERR_DEVICE; }
+  h->grid_max = h->grid;
   if (const char* g = getenv("DMS_TRACK_GRID")) {  // tuning knob: fewer co-resident CTAs than the maximum
     const int v = atoi(g);
     if (v > 0 && v < h->grid) h->grid = v;
@@ -221,6 +222,11 @@ int dms_odom_destroy(dms_odom* h) {
   return DMS_OK;
 }
 
+int dms_odom_set_grid(dms_odom* h, int n_ctas) {
+  if (!h || n_ctas < 0) return DMS_ERR_INVALID;
+  h->grid = (n_ctas == 0 || n_ctas > h->grid_max) ? h->grid_max : (n_ctas < 2 ? 2 : n_ctas);
+  return DMS_OK;
+}
 int dms_odom_set_timing(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->timing = enabled ? 1 : 0; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 

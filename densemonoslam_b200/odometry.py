@@ -233,6 +233,9 @@ class RGBDOdometry:
         self._ck(self._L.dms_odom_get_timeline(self._h, buf, 1024, C.byref(n)), "get_timeline")
         return [(int(buf[2 * i]), int(buf[2 * i + 1])) for i in range(n.value) if buf[2 * i + 1]]
 
+    def set_grid(self, n_ctas=0):
+        self._ck(self._L.dms_odom_set_grid(self._h, int(n_ctas)), "set_grid")
+
     def set_timing(self, enabled=True):
         self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")
 

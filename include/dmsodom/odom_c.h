@@ -69,6 +69,11 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
                     float distThresh, float angleThresh);
 int dms_odom_destroy(dms_odom* h);
 const char* dms_odom_last_error(const dms_odom* h);
+/* Limits the tracking kernel of this handle to `n_ctas` thread blocks (one per SM; 0 = all SMs).  Several handles
+ * (sensors, or frames of one open-loop sequence) whose limits add up to the SM count run their tracking kernels
+ * concurrently on one GPU, each on its own stream: the barrier / solve latency of one overlaps the pixel phases of
+ * the others.  Results do not depend on the limit (the reduction is order-free). */
+int dms_odom_set_grid(dms_odom* h, int n_ctas);
 int dms_odom_set_timing(dms_odom* h, int enabled);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
 
