@@ -10,13 +10,8 @@ namespace dms {
 // ---- pyramid.cu
 cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4, const float4* n4, int pitch4,
                                 const float* pose16_or_null, float* zdepth, float zcut, cudaStream_t s);
-cudaError_t launch_v2d_intensity(const float* zsrc, int pitch_z, float* depth, int pitch_d, const uchar4* rgba,
-                                 int pitch_rgba, unsigned char* img, int pitch_i, int rows, int cols, cudaStream_t s);
-cudaError_t launch_pyrdown_gauss(const float* sd, int spd, float* dd, int dpd, const unsigned char* si, int spi,
-                                 unsigned char* di, int dpi, int srows, int scols, cudaStream_t s);
-cudaError_t launch_pyrdown_u16(const unsigned short* src, int sp, unsigned short* dst, int dp, int srows, int scols,
-                               cudaStream_t s);
-cudaError_t launch_vmap_nmap(const Level* lv, float cutoff, cudaStream_t s);
+cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, cudaStream_t s);
+cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, cudaStream_t s);
 
 // ---- track.cu
 static const int ACC_STRIDE = 16;   // unsigned long long words between accumulator slots (128 B)

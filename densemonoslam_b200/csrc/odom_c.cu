@@ -79,18 +79,7 @@ void mat3_inv_host(const T* m, T* o) {  // same operation order as the oracle's 
 
 int populate(dms_odom* h, const uint8_t* d_rgba, size_t pitch, int which, cudaStream_t s) {
   // which: 0 = last (initRGBModel), 1 = next (initRGB), 2 = lastNext image only (initFirstRGB)
-  Level* L = h->lv;
-  float* d0 = which == 0 ? L[0].lastDepth : which == 1 ? L[0].nextDepth : nullptr;
-  unsigned char* i0 = which == 0 ? L[0].lastImage : which == 1 ? L[0].nextImage : L[0].lastNextImage;
-  CK(launch_v2d_intensity(h->zdepth, L[0].pitch_f32, d0, L[0].pitch_f32, reinterpret_cast<const uchar4*>(d_rgba), (int)pitch, i0,
-                          L[0].pitch_u8, L[0].rows, L[0].cols, s));
-  for (int i = 0; i + 1 < 3; ++i) {
-    float* sd = which == 0 ? L[i].lastDepth : which == 1 ? L[i].nextDepth : nullptr;
-    float* dd = which == 0 ? L[i + 1].lastDepth : which == 1 ? L[i + 1].nextDepth : nullptr;
-    unsigned char* si = which == 0 ? L[i].lastImage : which == 1 ? L[i].nextImage : L[i].lastNextImage;
-    unsigned char* di = which == 0 ? L[i + 1].lastImage : which == 1 ? L[i + 1].nextImage : L[i + 1].lastNextImage;
-    CK(launch_pyrdown_gauss(sd, L[i].pitch_f32, dd, L[i + 1].pitch_f32, si, L[i].pitch_u8, di, L[i + 1].pitch_u8, L[i].rows, L[i].cols, s));
-  }
+  CK(launch_populate(h->lv, which, h->zdepth, reinterpret_cast<const uchar4*>(d_rgba), (int)pitch, s));
   return DMS_OK;
 }
 
@@ -235,11 +224,8 @@ int dms_odom_init_icp_depth(dms_odom* h, const uint16_t* d_depth, size_t pitch, 
   if (!h || !d_depth) return fail(h, DMS_ERR_INVALID, "init_icp_depth: null argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  Level* L = h->lv;
   if (pitch == 0) pitch = (size_t)h->width * 2;
-  CK(cudaMemcpy2DAsync(L[0].depth_tmp, L[0].pitch_u16, d_depth, pitch, (size_t)L[0].cols * 2, L[0].rows, cudaMemcpyDeviceToDevice, s));
-  for (int i = 1; i < 3; ++i) CK(launch_pyrdown_u16(L[i - 1].depth_tmp, L[i - 1].pitch_u16, L[i].depth_tmp, L[i].pitch_u16, L[i - 1].rows, L[i - 1].cols, s));
-  CK(launch_vmap_nmap(L, depthCutoff, s));
+  CK(launch_icp_depth(h->lv, d_depth, (int)pitch, depthCutoff, s));
   return DMS_OK;
 }
 

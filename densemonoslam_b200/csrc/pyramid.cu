@@ -1,9 +1,7 @@
 // Pyramid construction kernels (reference kernels K1..K12), fused:
 //   maps_pyramid     : copyMaps + resizeVMap/resizeNMap x2 + tranformMaps      (cf.cu:313-354,445-492,200-246)
-//   v2d_intensity    : verticesToDepth + bgr2Intensity                         (cf.cu:597-608,643-655)
-//   pyrdown_gauss    : pyrDownGaussF + pyrDownUcharGauss                       (cf.cu:416-443,544-573)
-//   pyrdown_u16      : pyrDown (bilateral-ish u16 depth)                       (cf.cu:57-91)
-//   vmap_nmap        : createVMap + createNMap for the three levels            (cf.cu:106-128,149-182)
+//   populate         : verticesToDepth + bgr2Intensity + pyrDownGaussF x2 + pyrDownUcharGauss x2   (cf.cu:416-443,544-573,597-655)
+//   icp_depth        : pyrDown x2 (bilateral-ish u16) + createVMap + createNMap for the three levels   (cf.cu:57-182)
 // All outputs are bit-identical to running the reference's separate passes with IEEE arithmetic.
 #include "common.cuh"
 #include "kernels.h"
@@ -116,124 +114,129 @@ cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4
   return cudaGetLastError();
 }
 
-// ------------------------------------------------------------------ v2d_intensity
-// One thread per 4 consecutive pixels.  depth: the level-0 depth of the last loaded vertex map (already cut at
-// maxDepthRGB = 6 m by maps_pyramid; cf.cu:604-607, RO.cpp:37,213) is copied into the destination pyramid;
-// intensity: int(x*0.114f + y*0.299f + z*0.587f) = trunc(fma(z,.587, fma(x,.114, y*.299)))  (cf.cu:651-654)
-__global__ void __launch_bounds__(256) k_v2d_intensity(const float* zsrc, int pitch_z, float* depth, int pitch_d,
-                                                       const uchar4* rgba, int pitch_rgba, unsigned char* img, int pitch_i,
-                                                       int rows, int cols) {
-  const int qx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y;
-  const int x0 = qx * 4;
-  if (x0 >= cols || y >= rows) return;
-  const int n = min(4, cols - x0);
-  if (depth) {
-    float d[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-      d[p] = qnan();
-      if (p < n) d[p] = __ldg(row_ptr(zsrc, pitch_z, y) + x0 + p);
-    }
-    float* dr = row_ptr(depth, pitch_d, y) + x0;
-    if (n == 4) *reinterpret_cast<float4*>(dr) = make_float4(d[0], d[1], d[2], d[3]);
-    else for (int p = 0; p < n; ++p) dr[p] = d[p];
-  }
-  if (img) {
-    unsigned char o[4];
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-      o[p] = 0;
-      if (p < n) {
-        const uchar4 s = __ldg(row_ptr(rgba, pitch_rgba, y) + x0 + p);
-        const float v = ffma((float)s.z, 0.587f, ffma((float)s.x, 0.114f, fmul((float)s.y, 0.299f)));
-        o[p] = (unsigned char)__float2int_rz(v);
-      }
-    }
-    unsigned char* ir = row_ptr(img, pitch_i, y) + x0;
-    if (n == 4) *reinterpret_cast<uchar4*>(ir) = make_uchar4(o[0], o[1], o[2], o[3]);
-    else for (int p = 0; p < n; ++p) ir[p] = o[p];
-  }
-}
-
-cudaError_t launch_v2d_intensity(const float* zsrc, int pitch_z, float* depth, int pitch_d, const uchar4* rgba,
-                                 int pitch_rgba, unsigned char* img, int pitch_i, int rows, int cols, cudaStream_t s) {
-  const dim3 block(256);
-  const dim3 grid(((cols + 3) / 4 + 255) / 256, rows);
-  k_v2d_intensity<<<grid, block, 0, s>>>(zsrc, pitch_z, depth, pitch_d, rgba, pitch_rgba, img, pitch_i, rows, cols);
-  return cudaGetLastError();
-}
-
-// ------------------------------------------------------------------ pyrdown_gauss (f32 depth + u8 image)
+// ------------------------------------------------------------------ populate: depth + intensity pyramids in ONE launch
+// verticesToDepth copy + bgr2Intensity (cf.cu:597-608,643-655) and both levels of pyrDownGaussF / pyrDownUcharGauss
+// (cf.cu:416-443,544-573).  A CTA owns a 32x32 block of level 0 (= 16x16 of level 1 = 8x8 of level 2) and stages the
+// 41x41 / 19x19 tiles it needs (with halos) in shared memory, so every tap is a shared-memory read and the colour
+// image is read once.  Window bounds and weight indexing are the reference's, evaluated on global
+// coordinates, so results are bit-identical to the three separate passes.
 __constant__ float c_gauss5[25] = {1, 4, 6, 4, 1, 4, 16, 24, 16, 4, 6, 24, 36, 24, 6, 4, 16, 24, 16, 4, 1, 4, 6, 4, 1};
 
-__global__ void __launch_bounds__(256) k_pyrdown_gauss(const float* sd, int spd, float* dd, int dpd, const unsigned char* si,
-                                                       int spi, unsigned char* di, int dpi, int srows, int scols) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  const int drows = srows / 2, dcols = scols / 2;
-  if (x >= dcols || y >= drows) return;
-  const int tx = min(2 * x - 2 + 5, scols - 1);
-  const int ty = min(2 * y - 2 + 5, srows - 1);
-  const int cx0 = max(0, 2 * x - 2), cy0 = max(0, 2 * y - 2);
-  if (sd) {
-    float sum = 0.0f; int count = 0;
-    for (int cy = cy0; cy < ty; ++cy) {
-      const float* r = row_ptr(sd, spd, cy);
-      for (int cx = cx0; cx < tx; ++cx) {
-        const float v = __ldg(r + cx);
-        if (!isnan(v)) {
-          const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
-          sum = ffma(v, g, sum);
-          count = __float2int_rz(fadd((float)count, g));
-        }
-      }
+struct PopArgs {
+  const float* zsrc; int pitch_z;            // level-0 depth of the last loaded vertex map (already cut at 6 m)
+  const uchar4* rgba; int pitch_rgba;
+  float* depth[3]; unsigned char* img[3];    // destination pyramids (depth[] all null: image only)
+  int pitch_f[3], pitch_i[3], rows[3], cols[3];
+};
+
+template <bool HAS_DEPTH>
+__global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
+  __shared__ float sd0[41][41];
+  __shared__ unsigned char si0[41][44];
+  __shared__ float sd1[19][19];
+  __shared__ unsigned char si1[19][20];
+  const int tid = threadIdx.x, bx = blockIdx.x, by = blockIdx.y;
+  const int ox0 = 32 * bx - 6, oy0 = 32 * by - 6, ox1 = 16 * bx - 2, oy1 = 16 * by - 2;
+  // ---- level 0 tile (+ own 32x32 block written out)
+  for (int idx = tid; idx < 41 * 41; idx += 256) {
+    const int ly = idx / 41, lx = idx - ly * 41, gx = ox0 + lx, gy = oy0 + ly;
+    if (gx < 0 || gy < 0 || gx >= a.cols[0] || gy >= a.rows[0]) continue;
+    const uchar4 c = __ldg(row_ptr(a.rgba, a.pitch_rgba, gy) + gx);
+    const unsigned char iv = (unsigned char)__float2int_rz(ffma((float)c.z, 0.587f, ffma((float)c.x, 0.114f, fmul((float)c.y, 0.299f))));
+    si0[ly][lx] = iv;
+    float d = 0.f;
+    if (HAS_DEPTH) { d = __ldg(row_ptr(a.zsrc, a.pitch_z, gy) + gx); sd0[ly][lx] = d; }
+    if (lx >= 6 && lx < 38 && ly >= 6 && ly < 38) {
+      row_ptr(a.img[0], a.pitch_i[0], gy)[gx] = iv;
+      if (HAS_DEPTH) row_ptr(a.depth[0], a.pitch_f[0], gy)[gx] = d;
     }
-    row_ptr(dd, dpd, y)[x] = fdiv(sum, (float)count);
   }
-  if (si) {
-    float sum = 0.0f; int count = 0;
-    for (int cy = cy0; cy < ty; ++cy) {
-      const unsigned char* r = row_ptr(si, spi, cy);
+  __syncthreads();
+  // ---- level 1 tile
+  for (int idx = tid; idx < 19 * 19; idx += 256) {
+    const int ly = idx / 19, lx = idx - ly * 19, x = ox1 + lx, y = oy1 + ly;
+    if (x < 0 || y < 0 || x >= a.cols[1] || y >= a.rows[1]) continue;
+    const int tx = min(2 * x - 2 + 5, a.cols[0] - 1), ty = min(2 * y - 2 + 5, a.rows[0] - 1);
+    const int cx0 = max(0, 2 * x - 2), cy0 = max(0, 2 * y - 2);
+    float sumd = 0.f, sumi = 0.f; int cntd = 0, cnti = 0;
+    for (int cy = cy0; cy < ty; ++cy)
       for (int cx = cx0; cx < tx; ++cx) {
-        const unsigned char v = __ldg(r + cx);
-        if (v > 0) {
-          const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
-          sum = ffma((float)(int)v, g, sum);
-          count = __float2int_rz(fadd((float)count, g));
+        const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
+        const unsigned char iv = si0[cy - oy0][cx - ox0];
+        if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti = __float2int_rz(fadd((float)cnti, g)); }
+        if (HAS_DEPTH) {
+          const float v = sd0[cy - oy0][cx - ox0];
+          if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd = __float2int_rz(fadd((float)cntd, g)); }
         }
       }
+    const unsigned char iv1 = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));  // 0/0 -> NaN -> 0
+    si1[ly][lx] = iv1;
+    float d1 = 0.f;
+    if (HAS_DEPTH) { d1 = fdiv(sumd, (float)cntd); sd1[ly][lx] = d1; }
+    if (lx >= 2 && lx < 18 && ly >= 2 && ly < 18) {
+      row_ptr(a.img[1], a.pitch_i[1], y)[x] = iv1;
+      if (HAS_DEPTH) row_ptr(a.depth[1], a.pitch_f[1], y)[x] = d1;
     }
-    const float r = fdiv(sum, (float)count);  // 0/0 -> NaN -> 0
-    row_ptr(di, dpi, y)[x] = (unsigned char)__float2int_rz(r);
+  }
+  __syncthreads();
+  // ---- level 2 block
+  if (tid < 64) {
+    const int ly = tid >> 3, lx = tid & 7, x = 8 * bx + lx, y = 8 * by + ly;
+    if (x < a.cols[2] && y < a.rows[2]) {
+      const int tx = min(2 * x - 2 + 5, a.cols[1] - 1), ty = min(2 * y - 2 + 5, a.rows[1] - 1);
+      const int cx0 = max(0, 2 * x - 2), cy0 = max(0, 2 * y - 2);
+      float sumd = 0.f, sumi = 0.f; int cntd = 0, cnti = 0;
+      for (int cy = cy0; cy < ty; ++cy)
+        for (int cx = cx0; cx < tx; ++cx) {
+          const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
+          const unsigned char iv = si1[cy - oy1][cx - ox1];
+          if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti = __float2int_rz(fadd((float)cnti, g)); }
+          if (HAS_DEPTH) {
+            const float v = sd1[cy - oy1][cx - ox1];
+            if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd = __float2int_rz(fadd((float)cntd, g)); }
+          }
+        }
+      row_ptr(a.img[2], a.pitch_i[2], y)[x] = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));
+      if (HAS_DEPTH) row_ptr(a.depth[2], a.pitch_f[2], y)[x] = fdiv(sumd, (float)cntd);
+    }
   }
 }
 
-cudaError_t launch_pyrdown_gauss(const float* sd, int spd, float* dd, int dpd, const unsigned char* si, int spi,
-                                 unsigned char* di, int dpi, int srows, int scols, cudaStream_t s) {
-  const dim3 block(32, 8);
-  const dim3 grid((scols / 2 + 31) / 32, (srows / 2 + 7) / 8);
-  if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  k_pyrdown_gauss<<<grid, block, 0, s>>>(sd, spd, dd, dpd, si, spi, di, dpi, srows, scols);
+cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, cudaStream_t s) {
+  // which: 0 = last (initRGBModel), 1 = next (initRGB), 2 = lastNext image only (initFirstRGB)
+  PopArgs a;
+  a.zsrc = zsrc; a.pitch_z = lv[0].pitch_f32; a.rgba = rgba; a.pitch_rgba = pitch_rgba;
+  for (int i = 0; i < 3; ++i) {
+    a.depth[i] = which == 0 ? lv[i].lastDepth : which == 1 ? lv[i].nextDepth : nullptr;
+    a.img[i] = which == 0 ? lv[i].lastImage : which == 1 ? lv[i].nextImage : lv[i].lastNextImage;
+    a.pitch_f[i] = lv[i].pitch_f32; a.pitch_i[i] = lv[i].pitch_u8; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols;
+  }
+  const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 31) / 32);
+  if (which == 2) k_populate<false><<<grid, 256, 0, s>>>(a);
+  else k_populate<true><<<grid, 256, 0, s>>>(a);
   return cudaGetLastError();
 }
 
-// ------------------------------------------------------------------ pyrdown_u16 (cf.cu:57-91, sigma_color 30)
-__global__ void __launch_bounds__(256) k_pyrdown_u16(const unsigned short* src, int sp, unsigned short* dst, int dp, int srows,
-                                                     int scols) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y * blockDim.y + threadIdx.y;
-  const int drows = srows / 2, dcols = scols / 2;
-  if (x >= dcols || y >= drows) return;
-  const int center = __ldg(row_ptr(src, sp, 2 * y) + 2 * x);
+// ------------------------------------------------------------------ icp_depth: depth pyramid + vertex / normal maps in ONE launch
+// pyrDown x2 (cf.cu:57-91, sigma_color 30), createVMap and createNMap for the three levels (cf.cu:106-182).
+// Same tiling: 45x45 / 21x21 / 9x9 shared-memory tiles of u16 depth (one extra row / column for the forward
+// differences of the normals).
+struct IcpDepthArgs {
+  const unsigned short* depth; int pitch_in;
+  unsigned short* dt[3]; float* vmap[3]; float* nmap[3];
+  int pitch_u16[3], pitch_f[3], rows[3], cols[3];
+  Intr k[3]; float cutoff;
+};
+
+__device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* tile, int tstride, int ox, int oy, int x, int y, int srows, int scols) {
+  const int center = tile[(2 * y - oy) * tstride + (2 * x - ox)];
   const int x_mi = max(0, 2 * x - 2) - 2 * x, y_mi = max(0, 2 * y - 2) - 2 * y;
   const int x_ma = min(scols, 2 * x - 2 + 5) - 2 * x, y_ma = min(srows, 2 * y - 2 + 5) - 2 * y;
   float sum = 0.0f, wall = 0.0f;
   for (int yi = y_mi; yi < y_ma; ++yi) {
-    const unsigned short* r = row_ptr(src, sp, 2 * y + yi);
     const float wy = (yi == 0) ? 0.375f : (abs(yi) == 1 ? 0.25f : 0.0625f);
     for (int xi = x_mi; xi < x_ma; ++xi) {
-      const int val = __ldg(r + 2 * x + xi);
+      const int val = tile[(2 * y + yi - oy) * tstride + (2 * x + xi - ox)];
       if ((float)abs(val - center) < 90.0f) {
         const float wx = (xi == 0) ? 0.375f : (abs(xi) == 1 ? 0.25f : 0.0625f);
         sum = ffma(fmul((float)val, wx), wy, sum);
@@ -241,57 +244,79 @@ __global__ void __launch_bounds__(256) k_pyrdown_u16(const unsigned short* src, 
       }
     }
   }
-  row_ptr(dst, dp, y)[x] = (unsigned short)__float2int_rz(fdiv(sum, wall));
+  return (unsigned short)__float2int_rz(fdiv(sum, wall));
 }
 
-cudaError_t launch_pyrdown_u16(const unsigned short* src, int sp, unsigned short* dst, int dp, int srows, int scols,
-                               cudaStream_t s) {
-  const dim3 block(32, 8);
-  const dim3 grid((scols / 2 + 31) / 32, (srows / 2 + 7) / 8);
-  if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  k_pyrdown_u16<<<grid, block, 0, s>>>(src, sp, dst, dp, srows, scols);
-  return cudaGetLastError();
-}
-
-// ------------------------------------------------------------------ vmap_nmap (all three levels, grid.z = level)
-struct VNArgs { const unsigned short* depth[3]; int pd[3]; float* vmap[3]; float* nmap[3]; int pf[3]; int rows[3]; int cols[3]; Intr k[3]; float cutoff; };
-
-__device__ __forceinline__ float3 backproject(const unsigned short* depth, int pd, int u, int v, const Intr& k, float fxi, float fyi,
-                                              float cutoff) {
-  const float z = fdiv((float)(int)__ldg(row_ptr(depth, pd, v) + u), 1000.f);
+__device__ __forceinline__ float3 backproject_d(int d, int u, int v, const Intr& k, float fxi, float fyi, float cutoff) {
+  const float z = fdiv((float)d, 1000.f);
   if (z != 0 && z < cutoff) return make_float3(fmul(fmul(z, fsub((float)u, k.cx)), fxi), fmul(fmul(z, fsub((float)v, k.cy)), fyi), z);
   return make_float3(qnan(), qnan(), qnan());
 }
 
-__global__ void __launch_bounds__(256) k_vmap_nmap(const VNArgs a) {
-  const int l = blockIdx.z;
-  const int u = blockIdx.x * blockDim.x + threadIdx.x;
-  const int v = blockIdx.y * blockDim.y + threadIdx.y;
-  const int rows = a.rows[l], cols = a.cols[l];
-  if (u >= cols || v >= rows) return;
-  const Intr k = a.k[l];
+// vertex + normal of the own block of one level from its shared depth tile
+__device__ __forceinline__ void vn_block(const unsigned short* tile, int tstride, int ox, int oy, int bx0, int by0, int bw, int rows, int cols,
+                                         const Intr& k, float cutoff, float* vmap, float* nmap, int pitch) {
   const float fxi = fdiv(1.f, k.fx), fyi = fdiv(1.f, k.fy);
-  const float3 v00 = backproject(a.depth[l], a.pd[l], u, v, k, fxi, fyi, a.cutoff);
-  store_plane3(a.vmap[l], a.pf[l], rows, v, u, v00);
-  float3 n = make_float3(qnan(), qnan(), qnan());
-  if (u < cols - 1 && v < rows - 1) {
-    const float3 v01 = backproject(a.depth[l], a.pd[l], u + 1, v, k, fxi, fyi, a.cutoff);
-    const float3 v10 = backproject(a.depth[l], a.pd[l], u, v + 1, k, fxi, fyi, a.cutoff);
-    if (!isnan(v00.x) && !isnan(v01.x) && !isnan(v10.x)) n = normalized3(cross3(sub3(v01, v00), sub3(v10, v00)));
+  for (int idx = threadIdx.x; idx < bw * bw; idx += blockDim.x) {
+    const int ly = idx / bw, lx = idx - ly * bw, u = bx0 + lx, v = by0 + ly;
+    if (u >= cols || v >= rows) continue;
+    const float3 v00 = backproject_d(tile[(v - oy) * tstride + (u - ox)], u, v, k, fxi, fyi, cutoff);
+    store_plane3(vmap, pitch, rows, v, u, v00);
+    float3 n = make_float3(qnan(), qnan(), qnan());
+    if (u < cols - 1 && v < rows - 1) {
+      const float3 v01 = backproject_d(tile[(v - oy) * tstride + (u + 1 - ox)], u + 1, v, k, fxi, fyi, cutoff);
+      const float3 v10 = backproject_d(tile[(v + 1 - oy) * tstride + (u - ox)], u, v + 1, k, fxi, fyi, cutoff);
+      if (!isnan(v00.x) && !isnan(v01.x) && !isnan(v10.x)) n = normalized3(cross3(sub3(v01, v00), sub3(v10, v00)));
+    }
+    store_plane3(nmap, pitch, rows, v, u, n);
   }
-  store_plane3(a.nmap[l], a.pf[l], rows, v, u, n);
 }
 
-cudaError_t launch_vmap_nmap(const Level* lv, float cutoff, cudaStream_t s) {
-  VNArgs a;
-  for (int i = 0; i < 3; ++i) {
-    a.depth[i] = lv[i].depth_tmp; a.pd[i] = lv[i].pitch_u16; a.vmap[i] = lv[i].vmap_curr; a.nmap[i] = lv[i].nmap_curr;
-    a.pf[i] = lv[i].pitch_f32; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols; a.k[i] = lv[i].intr;
+__global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
+  __shared__ unsigned short t0[45 * 46];
+  __shared__ unsigned short t1[21 * 22];
+  __shared__ unsigned short t2[9 * 10];
+  const int tid = threadIdx.x, bx = blockIdx.x, by = blockIdx.y;
+  const int ox0 = 32 * bx - 6, oy0 = 32 * by - 6, ox1 = 16 * bx - 2, oy1 = 16 * by - 2, ox2 = 8 * bx, oy2 = 8 * by;
+  for (int idx = tid; idx < 45 * 45; idx += 256) {
+    const int ly = idx / 45, lx = idx - ly * 45, gx = ox0 + lx, gy = oy0 + ly;
+    if (gx < 0 || gy < 0 || gx >= a.cols[0] || gy >= a.rows[0]) continue;
+    const unsigned short d = __ldg(row_ptr(a.depth, a.pitch_in, gy) + gx);
+    t0[ly * 46 + lx] = d;
+    if (lx >= 6 && lx < 38 && ly >= 6 && ly < 38) row_ptr(a.dt[0], a.pitch_u16[0], gy)[gx] = d;
   }
-  a.cutoff = cutoff;
-  const dim3 block(32, 8);
-  const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 7) / 8, 3);
-  k_vmap_nmap<<<grid, block, 0, s>>>(a);
+  __syncthreads();
+  for (int idx = tid; idx < 21 * 21; idx += 256) {
+    const int ly = idx / 21, lx = idx - ly * 21, x = ox1 + lx, y = oy1 + ly;
+    if (x < 0 || y < 0 || x >= a.cols[1] || y >= a.rows[1]) continue;
+    const unsigned short d = pyrdown_u16_tap(t0, 46, ox0, oy0, x, y, a.rows[0], a.cols[0]);
+    t1[ly * 22 + lx] = d;
+    if (lx >= 2 && lx < 18 && ly >= 2 && ly < 18) row_ptr(a.dt[1], a.pitch_u16[1], y)[x] = d;
+  }
+  __syncthreads();
+  if (tid < 81) {
+    const int ly = tid / 9, lx = tid - ly * 9, x = ox2 + lx, y = oy2 + ly;
+    if (x < a.cols[2] && y < a.rows[2]) {
+      const unsigned short d = pyrdown_u16_tap(t1, 22, ox1, oy1, x, y, a.rows[1], a.cols[1]);
+      t2[ly * 10 + lx] = d;
+      if (lx < 8 && ly < 8) row_ptr(a.dt[2], a.pitch_u16[2], y)[x] = d;
+    }
+  }
+  __syncthreads();
+  vn_block(t0, 46, ox0, oy0, 32 * bx, 32 * by, 32, a.rows[0], a.cols[0], a.k[0], a.cutoff, a.vmap[0], a.nmap[0], a.pitch_f[0]);
+  vn_block(t1, 22, ox1, oy1, 16 * bx, 16 * by, 16, a.rows[1], a.cols[1], a.k[1], a.cutoff, a.vmap[1], a.nmap[1], a.pitch_f[1]);
+  vn_block(t2, 10, ox2, oy2, 8 * bx, 8 * by, 8, a.rows[2], a.cols[2], a.k[2], a.cutoff, a.vmap[2], a.nmap[2], a.pitch_f[2]);
+}
+
+cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, cudaStream_t s) {
+  IcpDepthArgs a;
+  a.depth = d_depth; a.pitch_in = pitch_in; a.cutoff = cutoff;
+  for (int i = 0; i < 3; ++i) {
+    a.dt[i] = lv[i].depth_tmp; a.vmap[i] = lv[i].vmap_curr; a.nmap[i] = lv[i].nmap_curr;
+    a.pitch_u16[i] = lv[i].pitch_u16; a.pitch_f[i] = lv[i].pitch_f32; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols; a.k[i] = lv[i].intr;
+  }
+  const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 31) / 32);
+  k_icp_depth<<<grid, 256, 0, s>>>(a);
   return cudaGetLastError();
 }
 
