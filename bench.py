@@ -355,6 +355,14 @@ def main():
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
            "gpu_launches": 14 * args.steps, "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
            "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
+    if world > 1:
+        # the only exchange of the multi-sensor mode: per-frame result records, gathered on rank 0 outside the timed region
+        from densemonoslam_b200 import multi
+        rec = multi.pack_record(last[0], last[1], [pipe[0][0].lastICPError, pipe[0][0].lastICPCount, pipe[0][0].lastRGBError,
+                                                   pipe[0][0].lastRGBCount, pipe[0][0].lastSO3Error, pipe[0][0].lastSO3Count])
+        full = multi.gather_records({rank: rec[None]}, world, 1, device="cuda")
+        if rank == 0:
+            out["gathered_result_records"] = list(full.shape)
     if depth > 1 and world == 1:
         # the same sequence on one tracker owning the whole GPU: per-frame latency and the full-GPU kernel roofline
         del pipe
