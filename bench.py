@@ -126,8 +126,8 @@ class ClockSampler(threading.Thread):
 def run_oracle_frames(cam, frames, n_frames, budget_s, threads=None):
     """Times the CPU oracle on the same per-frame call sequence; returns (frames_done, seconds, threads)."""
     from oracle import oracle as orc
-    if threads:
-        orc.set_num_threads(threads)
+    # all host cores unless told otherwise (torchrun exports OMP_NUM_THREADS=1, which must not throttle the CPU arm)
+    orc.set_num_threads(threads if threads else len(os.sched_getaffinity(0)))
     o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
     o.initFirstRGB(frames[0]["live"]["rgba"])
     done, t0 = 0, time.perf_counter()
@@ -185,7 +185,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=3, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--pipeline", type=int, default=6, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -252,7 +253,7 @@ def main():
         hs, ss = [], []
         for k in range(depth):
             h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
-            h.set_grid(0 if depth == 1 else sms // depth)
+            h.set_grid(args.grid if args.grid else (0 if depth == 1 else sms // depth))
             h.set_timing(True)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss
