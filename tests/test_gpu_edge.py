@@ -1,0 +1,119 @@
+"""Edge cases of the path on the GPU, each against the CPU oracle: ragged sizes, empty inputs, pitched inputs,
+rotated poses, the 0.3 m guard, shared-GPU trackers."""
+import threading
+
+import numpy as np
+import pytest
+
+from conftest import assert_f32_equal
+from test_gpu_parity import FLAG_ROWS, both, check_pyramids, compare_track, load_frame_to_model, to_dev
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+@pytest.mark.parametrize("wh", [(323, 241), (97, 65), (64, 48)])
+def test_ragged_sizes(torch_cuda, orc, synth, wh):
+    """Widths / heights that are not multiples of 4, 32 or the pyramid factor (levels W>>1, W>>2)."""
+    w, h = wh
+    cam = synth.Camera(w, h, 0.8 * w, 0.8 * w, w / 2 - 0.5, h / 2 + 0.25)
+    model, live, T = synth.frame_pair(cam, seed=3, rvec=(0.004, -0.006, 0.003), tvec=(0.008, -0.004, 0.006))
+    g, o = both(orc, synth, cam)
+    pose = synth.pose_from((0.3, -0.2, 0.1), (0.5, -0.25, 1.0)).astype(np.float32)
+    load_frame_to_model(torch_cuda, g, o, model, live, pose)
+    g.initFirstRGB(to_dev(torch_cuda, model["rgba"])); o.initFirstRGB(model["rgba"])
+    check_pyramids(g, o)
+    compare_track(g, o, pose[:3, 3].copy(), pose[:3, :3].copy(), FLAG_ROWS["frameToModel"])
+
+
+def test_empty_inputs_give_the_same_nans(torch_cuda, orc, synth, pair_small):
+    """No depth, empty model: zero correspondences everywhere; the degenerate solve propagates NaN exactly as in the oracle."""
+    cam, model, live, T = pair_small
+    g, o = both(orc, synth, cam)
+    m = {k: np.zeros_like(v) for k, v in model.items()}
+    l = {k: np.zeros_like(v) for k, v in live.items()}
+    pose = np.eye(4, dtype=np.float32)
+    load_frame_to_model(torch_cuda, g, o, m, l, pose)
+    check_pyramids(g, o)
+    tg, Rg = g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["modelToModel"])
+    to_, Ro, res = o.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["modelToModel"])
+    assert g.lastICPCount == res.lastICPCount == 0 and g.lastRGBCount == res.lastRGBCount == 0
+    assert np.array_equal(tg, to_, equal_nan=True) and np.array_equal(Rg, Ro, equal_nan=True)
+    assert np.array_equal(np.isnan(g.lastA), np.isnan(np.array(res.A[:]).reshape(6, 6)))
+
+
+def test_pitched_device_inputs(torch_cuda, orc, synth, pair_small):
+    """Row pitch larger than the row (views into wider tensors), as a mapped texture can have."""
+    torch = torch_cuda
+    cam, model, live, T = pair_small
+    g, o = both(orc, synth, cam)
+
+    def pitched(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        wide = torch.zeros((t.shape[0], t.shape[1] + 24) + tuple(t.shape[2:]), dtype=t.dtype, device="cuda")
+        wide[:, : t.shape[1]] = t
+        return wide[:, : t.shape[1]]
+    pose = np.eye(4, dtype=np.float32)
+    g.initICPModel(pitched(model["vmap4"]), pitched(model["nmap4"]), 25.0, pose); g.initRGBModel(pitched(model["rgba"]))
+    g.initICP(pitched(live["depth"]), 25.0); g.initRGB(pitched(live["rgba"]))
+    o.initICPModel(model["vmap4"], model["nmap4"], pose); o.initRGBModel(model["rgba"]); o.initICP(live["depth"], 25.0); o.initRGB(live["rgba"])
+    check_pyramids(g, o)
+
+
+def test_translation_guard(torch_cuda, orc, synth):
+    """RO.cpp:589-593: an update of more than 0.3 m with an RGB term returns the input pose."""
+    cam = synth.scaled_camera(synth.CAM_VGA, 4)
+    model, live, T = synth.frame_pair(cam, seed=3, tvec=(0.9, 0.0, 0.0), rvec=(0, 0, 0))
+    g, o = both(orc, synth, cam)
+    pose = np.eye(4, dtype=np.float32)
+    load_frame_to_model(torch_cuda, g, o, model, live, pose)
+    t, R = compare_track(g, o, pose[:3, 3], pose[:3, :3], FLAG_ROWS["modelToModel"])
+    assert np.linalg.norm(t) <= 0.3 + 1e-6
+
+
+def test_depth_cutoff_and_thresholds(torch_cuda, orc, synth, pair_small):
+    """Non-default distThresh and a depth cutoff inside the scene."""
+    cam, model, live, T = pair_small
+    g, o = both(orc, synth, cam, distThresh=0.03)
+    pose = np.eye(4, dtype=np.float32)
+    cv = lambda a: to_dev(torch_cuda, a)
+    g.initICPModel(cv(model["vmap4"]), cv(model["nmap4"]), 25.0, pose); o.initICPModel(model["vmap4"], model["nmap4"], pose)
+    g.initRGBModel(cv(model["rgba"])); o.initRGBModel(model["rgba"])
+    g.initICP(cv(live["depth"]), 3.0); o.initICP(live["depth"], 3.0)
+    g.initRGB(cv(live["rgba"])); o.initRGB(live["rgba"])
+    check_pyramids(g, o)
+    compare_track(g, o, pose[:3, 3], pose[:3, :3], FLAG_ROWS["modelToModel"])
+
+
+def test_trackers_sharing_the_gpu_are_independent_and_exact(torch_cuda, orc, synth, pair_small):
+    """Two handles, own streams, each limited to half the SMs, driven from two host threads at once:
+    every result equals the oracle's (the reduction does not depend on the grid)."""
+    torch = torch_cuda
+    cam, model, live, T = pair_small
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    pose = np.eye(4, dtype=np.float32)
+    o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+    o.initFirstRGB(model["rgba"]); o.initICPModel(model["vmap4"], model["nmap4"], pose); o.initRGBModel(model["rgba"]); o.initICP(live["depth"], 25.0); o.initRGB(live["rgba"])
+    to_, Ro, res = o.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["frameToModel"])
+    from densemonoslam_b200.odometry import RGBDOdometry
+    dev = {k: to_dev(torch, v) for k, v in (("v", model["vmap4"]), ("n", model["nmap4"]), ("mi", model["rgba"]), ("d", live["depth"]), ("li", live["rgba"]))}
+    outs = [None, None]
+
+    def work(k):
+        h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+        h.set_grid(sms // 2)
+        s = torch.cuda.Stream()
+        for _ in range(5):
+            h.initFirstRGB(dev["mi"], stream=s); h.initICPModel(dev["v"], dev["n"], 25.0, pose, stream=s); h.initRGBModel(dev["mi"], stream=s)
+            h.initICP(dev["d"], 25.0, stream=s); h.initRGB(dev["li"], stream=s)
+            outs[k] = h.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["frameToModel"], stream=s) + (h.lastICPCount, h.lastRGBCount)
+    ths = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    [t.start() for t in ths]; [t.join() for t in ths]
+    for t, R, ci, cr in outs:
+        assert np.array_equal(t, to_) and np.array_equal(R, Ro) and ci == res.lastICPCount and cr == res.lastRGBCount
