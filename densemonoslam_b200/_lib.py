@@ -73,6 +73,8 @@ SIGNATURES = {
     "dms_odom_rgb_step": (C.c_int, [_P, C.c_int, C.c_float, _F3, C.POINTER(C.c_int64), _P]),
     "dms_odom_so3_step": (C.c_int, [_P, C.c_int, _F3, _F3, _F3, _F3, C.POINTER(C.c_int64), _P]),
     "dms_odom_compute_derivatives": (C.c_int, [_P, _P]),
+    "dms_depth_bilateral": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_float, _P, C.c_size_t, _P]),
+    "dms_depth_metric": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_float, _P, C.c_size_t, _P]),
     "dms_icp_step_noalloc": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                        _F3, _F3, _F3, _F3, C.c_float, C.c_float, _P, _P]),
     "dms_version": (C.c_char_p, []),

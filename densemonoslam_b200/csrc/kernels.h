@@ -13,6 +13,9 @@ cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4
 cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, cudaStream_t s);
 cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, cudaStream_t s);
 
+cudaError_t launch_depth_bilateral(const unsigned short* src, int sp, unsigned short* dst, int dp, int rows, int cols, float maxD, cudaStream_t s);
+cudaError_t launch_depth_metric(const unsigned short* src, int sp, float* dst, int dp, int rows, int cols, float maxD, cudaStream_t s);
+
 // ---- track.cu
 static const int ACC_STRIDE = 16;   // unsigned long long words between accumulator slots (128 B)
 static const int ACC_SLOTS = 192;

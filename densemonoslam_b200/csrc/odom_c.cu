@@ -515,6 +515,21 @@ int dms_odom_icp_residual(dms_odom* h, const float trans_curr[3], const float ro
   return DMS_OK;
 }
 
+// ------------------------------------------------------------------ depth pre-filter (stateless)
+int dms_depth_bilateral(const uint16_t* d_raw, size_t pitch_in, int rows, int cols, float maxDepth, uint16_t* d_filtered, size_t pitch_out,
+                        void* stream) {
+  if (!d_raw || !d_filtered || rows <= 0 || cols <= 0) return DMS_ERR_INVALID;
+  cudaError_t e = launch_depth_bilateral(d_raw, (int)(pitch_in ? pitch_in : (size_t)cols * 2), d_filtered, (int)(pitch_out ? pitch_out : (size_t)cols * 2),
+                                         rows, cols, maxDepth, (cudaStream_t)stream);
+  return e == cudaSuccess ? DMS_OK : (int)e;
+}
+int dms_depth_metric(const uint16_t* d_raw, size_t pitch_in, int rows, int cols, float maxDepth, float* d_metres, size_t pitch_out, void* stream) {
+  if (!d_raw || !d_metres || rows <= 0 || cols <= 0) return DMS_ERR_INVALID;
+  cudaError_t e = launch_depth_metric(d_raw, (int)(pitch_in ? pitch_in : (size_t)cols * 2), d_metres, (int)(pitch_out ? pitch_out : (size_t)cols * 4), rows,
+                                      cols, maxDepth, (cudaStream_t)stream);
+  return e == cudaSuccess ? DMS_OK : (int)e;
+}
+
 // ------------------------------------------------------------------ buffers
 int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t* pitch, int* rows, int* cols, int* elem) {
   if (!h || level < 0 || level > 2) return fail(h, DMS_ERR_INVALID, "get_buffer: bad argument");

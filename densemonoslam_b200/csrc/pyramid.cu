@@ -320,4 +320,70 @@ cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ depth pre-filter (the step before initICP(depth))
+// exp(-t), t >= 0, in explicit fp32 steps (bit-identical to the oracle's; GLSL's exp is implementation defined)
+__device__ __forceinline__ float exp_neg(float t) {
+  const float a = fmul(t, 1.44269504f);
+  const float n = rintf(a);
+  if (!(n < 126.0f)) return 0.0f;
+  const float f = fsub(a, n);
+  float p = 1.54035304e-4f;
+  p = ffma(p, f, -1.33335581e-3f);
+  p = ffma(p, f, 9.61812911e-3f);
+  p = ffma(p, f, -5.55041087e-2f);
+  p = ffma(p, f, 2.40226507e-1f);
+  p = ffma(p, f, -6.93147181e-1f);
+  p = ffma(p, f, 1.0f);
+  return fmul(p, __int_as_float((127 - (int)n) << 23));
+}
+
+// Shaders/depth_bilateral.frag:31-75: 13x13 bilateral filter on raw u16 millimetres.  32x8 outputs per CTA from a
+// 44x20 shared tile.
+__global__ void __launch_bounds__(256) k_depth_bilateral(const unsigned short* src, int sp, unsigned short* dst, int dp, int rows, int cols,
+                                                         float maxD) {
+  __shared__ unsigned short tile[20][46];
+  const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 8;
+  for (int idx = threadIdx.x; idx < 20 * 44; idx += 256) {
+    const int ly = idx / 44, lx = idx - ly * 44, gx = x0 - 6 + lx, gy = y0 - 6 + ly;
+    tile[ly][lx] = (gx >= 0 && gy >= 0 && gx < cols && gy < rows) ? __ldg(row_ptr(src, sp, gy) + gx) : (unsigned short)0;
+  }
+  __syncthreads();
+  const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5, x = x0 + lx, y = y0 + ly;
+  if (x >= cols || y >= rows) return;
+  const unsigned int value = tile[ly + 6][lx + 6];
+  const unsigned int hi = (unsigned int)fmul(maxD, 1000.0f);
+  if (value > hi || value < 300U) { row_ptr(dst, dp, y)[x] = 0; return; }
+  const int tx = min(x - 6 + 13, cols), ty = min(y - 6 + 13, rows);
+  float sum1 = 0.f, sum2 = 0.f;
+  for (int cy = max(y - 6, 0); cy < ty; ++cy)
+    for (int cx = max(x - 6, 0); cx < tx; ++cx) {
+      const unsigned int tmp = tile[cy - y0 + 6][cx - x0 + 6];
+      const float dx = fsub((float)x, (float)cx), dy = fsub((float)y, (float)cy);
+      const float space2 = ffma(dx, dx, fmul(dy, dy));
+      const float dc = fsub((float)value, (float)tmp);
+      const float weight = exp_neg(ffma(space2, 0.024691358f, fmul(fmul(dc, dc), 0.000555556f)));
+      sum1 = ffma((float)tmp, weight, sum1);
+      sum2 = fadd(sum2, weight);
+    }
+  row_ptr(dst, dp, y)[x] = (unsigned short)(unsigned int)roundf(fdiv(sum1, sum2));
+}
+
+// Shaders/depth_metric.frag:29-39
+__global__ void __launch_bounds__(256) k_depth_metric(const unsigned short* src, int sp, float* dst, int dp, int rows, int cols, float maxD) {
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= cols || y >= rows) return;
+  const unsigned int value = __ldg(row_ptr(src, sp, y) + x);
+  const unsigned int hi = (unsigned int)fmul(maxD, 1000.0f);
+  row_ptr(dst, dp, y)[x] = (value > hi || value < 300U) ? 0.0f : fdiv((float)value, 1000.0f);
+}
+
+cudaError_t launch_depth_bilateral(const unsigned short* src, int sp, unsigned short* dst, int dp, int rows, int cols, float maxD, cudaStream_t s) {
+  k_depth_bilateral<<<dim3((cols + 31) / 32, (rows + 7) / 8), 256, 0, s>>>(src, sp, dst, dp, rows, cols, maxD);
+  return cudaGetLastError();
+}
+cudaError_t launch_depth_metric(const unsigned short* src, int sp, float* dst, int dp, int rows, int cols, float maxD, cudaStream_t s) {
+  k_depth_metric<<<dim3((cols + 31) / 32, (rows + 7) / 8), 256, 0, s>>>(src, sp, dst, dp, rows, cols, maxD);
+  return cudaGetLastError();
+}
+
 }  // namespace dms

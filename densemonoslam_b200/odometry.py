@@ -292,3 +292,27 @@ def device_count():
 
 def version():
     return _lib.load().dms_version().decode()
+
+
+def filterDepth(raw, maxDepth, stream=None):
+    """ElasticFusion::filterDepth (EF.cpp:759-768): raw u16 mm CUDA tensor [H, W] -> bilateral-filtered u16 mm tensor."""
+    import torch
+    L = _lib.load()
+    out = torch.empty_like(raw)
+    rc = L.dms_depth_bilateral(C.c_void_p(raw.data_ptr()), raw.stride(0) * 2, raw.shape[0], raw.shape[1], float(maxDepth), C.c_void_p(out.data_ptr()),
+                               out.stride(0) * 2, RGBDOdometry._stream(stream))
+    if rc != 0:
+        raise DmsError(f"dms_depth_bilateral failed ({rc})")
+    return out
+
+
+def metriciseDepth(raw, maxDepth, stream=None):
+    """ElasticFusion::metriciseDepth (EF.cpp:748-757): u16 mm CUDA tensor -> f32 metres tensor."""
+    import torch
+    L = _lib.load()
+    out = torch.empty(raw.shape, dtype=torch.float32, device=raw.device)
+    rc = L.dms_depth_metric(C.c_void_p(raw.data_ptr()), raw.stride(0) * 2, raw.shape[0], raw.shape[1], float(maxDepth), C.c_void_p(out.data_ptr()),
+                            out.stride(0) * 4, RGBDOdometry._stream(stream))
+    if rc != 0:
+        raise DmsError(f"dms_depth_metric failed ({rc})")
+    return out

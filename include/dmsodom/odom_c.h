@@ -173,6 +173,17 @@ int dms_odom_so3_step(dms_odom* h, int level, const float imageBasis[9], const f
  * iteration-invariant photometric candidate mask used by rgb_residual). */
 int dms_odom_compute_derivatives(dms_odom* h, void* stream);
 
+/* ---- depth pre-filter: the step immediately before initICP(depth).  Stateless, device pointers.
+ * ElasticFusion::filterDepth  (ElasticFusion.cpp:759-768, Shaders/depth_bilateral.frag:31-75): 13x13 bilateral filter on
+ *   raw u16 millimetres, values < 300 or > maxDepth*1000 -> 0, uint(round(.)).  exp() is evaluated in explicit fp32 steps so
+ *   the result is reproducible (GLSL's exp is implementation defined; parity with the GL shader is therefore unpinned).
+ * ElasticFusion::metriciseDepth (ElasticFusion.cpp:748-757, Shaders/depth_metric.frag:29-39): millimetres -> metres with
+ *   the same validity test. */
+int dms_depth_bilateral(const uint16_t* d_raw, size_t pitch_in, int rows, int cols, float maxDepth, uint16_t* d_filtered,
+                        size_t pitch_out, void* stream);
+int dms_depth_metric(const uint16_t* d_raw, size_t pitch_in, int rows, int cols, float maxDepth, float* d_metres,
+                     size_t pitch_out, void* stream);
+
 /* ---- allocation-free variant of the ICP step.  NO COUNTERPART IN THE REFERENCE.
  *
  * For callers that are not allowed to allocate device memory: a tracker hosted inside another

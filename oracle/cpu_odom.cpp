@@ -376,6 +376,65 @@ static void derivatives(const uint8_t* src, int rows, int cols, int16_t* dx, int
     }
 }
 
+// ------------------------------------------------------------------ depth pre-filter (the step before initICP(depth))
+
+// exp(-t), t >= 0, as plain fp32 arithmetic so that CPU and GPU agree bit for bit (GLSL's exp is implementation
+// defined; this one is accurate to ~3e-7 relative): 2^(-a), a = t*log2(e) = n + f with n = rint(a), 2^(-f) by its
+// degree-6 Taylor polynomial.
+static inline float exp_neg(float t) {
+  const float a = t * 1.44269504f;
+  const float n = nearbyintf(a);     // ties to even, as rintf on the GPU
+  if (!(n < 126.0f)) return 0.0f;    // also catches NaN
+  const float f = a - n;             // [-0.5, 0.5]
+  float p = 1.54035304e-4f;          // Taylor series of 2^(-f) = exp(-f ln 2), degree 6 (truncation 1.2e-7)
+  p = fmaf(p, f, -1.33335581e-3f);
+  p = fmaf(p, f, 9.61812911e-3f);
+  p = fmaf(p, f, -5.55041087e-2f);
+  p = fmaf(p, f, 2.40226507e-1f);
+  p = fmaf(p, f, -6.93147181e-1f);
+  p = fmaf(p, f, 1.0f);
+  uint32_t bits = (uint32_t)(127 - (int)n) << 23;  // 2^(-n)
+  float s; memcpy(&s, &bits, 4);
+  return p * s;
+}
+
+// Shaders/depth_bilateral.frag:31-75 (ElasticFusion::filterDepth, ElasticFusion.cpp:759-768): 13x13 bilateral filter
+// on raw u16 millimetres; texel (cx, cy) is read for the tap at (cx, cy).
+static void depth_bilateral(const uint16_t* src, int rows, int cols, float maxD, uint16_t* dst) {
+  const float ss = 0.024691358f, sc = 0.000555556f;
+  const unsigned int hi = (unsigned int)(maxD * 1000.0f);
+#pragma omp parallel for schedule(static)
+  for (int y = 0; y < rows; ++y)
+    for (int x = 0; x < cols; ++x) {
+      const unsigned int value = src[(size_t)y * cols + x];
+      if (value > hi || value < 300U) { dst[(size_t)y * cols + x] = 0; continue; }
+      const int tx = std::min(x - 6 + 13, cols), ty = std::min(y - 6 + 13, rows);
+      float sum1 = 0, sum2 = 0;
+      for (int cy = std::max(y - 6, 0); cy < ty; ++cy)
+        for (int cx = std::max(x - 6, 0); cx < tx; ++cx) {
+          const unsigned int tmp = src[(size_t)cy * cols + cx];
+          const float dx = (float)x - (float)cx, dy = (float)y - (float)cy;
+          const float space2 = fmaf(dx, dx, dy * dy);
+          const float dc = (float)value - (float)tmp;
+          const float color2 = dc * dc;
+          const float weight = exp_neg(fmaf(space2, ss, color2 * sc));
+          sum1 = fmaf((float)tmp, weight, sum1);
+          sum2 = sum2 + weight;
+        }
+      dst[(size_t)y * cols + x] = (uint16_t)(unsigned int)roundf(sum1 / sum2);
+    }
+}
+
+// Shaders/depth_metric.frag:29-39 (ElasticFusion::metriciseDepth, ElasticFusion.cpp:748-757)
+static void depth_metric(const uint16_t* src, int rows, int cols, float maxD, float* dst) {
+  const unsigned int hi = (unsigned int)(maxD * 1000.0f);
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < rows * cols; ++i) {
+    const unsigned int value = src[i];
+    dst[i] = (value > hi || value < 300U) ? 0.0f : (float)value / 1000.0f;
+  }
+}
+
 // ------------------------------------------------------------------ GN per-pixel terms
 
 struct Intr { float fx, fy, cx, cy; };
@@ -1002,6 +1061,9 @@ void orc_transform_maps(float* vmap, float* nmap, int rows, int cols, const floa
 }
 void orc_vertices_to_depth(const float* v4, int rows, int cols, float cutoff, float* dst) { vertices_to_depth(v4, rows, cols, cutoff, dst); }
 void orc_derivatives(const uint8_t* src, int rows, int cols, int16_t* dx, int16_t* dy) { derivatives(src, rows, cols, dx, dy); }
+void orc_depth_bilateral(const uint16_t* src, int rows, int cols, float maxD, uint16_t* dst) { depth_bilateral(src, rows, cols, maxD, dst); }
+void orc_depth_metric(const uint16_t* src, int rows, int cols, float maxD, float* dst) { depth_metric(src, rows, cols, maxD, dst); }
+float orc_exp_neg(float t) { return exp_neg(t); }
 
 // out[28] products (27 JtJ/Jtr + residual), inliers
 void orc_icp_step(const float Rcurr[9], const float tcurr[3], const float* vmap_curr, const float* nmap_curr,

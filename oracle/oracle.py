@@ -160,6 +160,25 @@ def derivatives(img):
     return dx, dy
 
 
+def depth_bilateral(raw, maxD):
+    H, W = raw.shape
+    out = np.empty((H, W), np.uint16)
+    lib().orc_depth_bilateral(C.c_void_p(np.ascontiguousarray(raw, np.uint16).ctypes.data), H, W, C.c_float(maxD), C.c_void_p(out.ctypes.data))
+    return out
+
+
+def depth_metric(raw, maxD):
+    H, W = raw.shape
+    out = np.empty((H, W), np.float32)
+    lib().orc_depth_metric(C.c_void_p(np.ascontiguousarray(raw, np.uint16).ctypes.data), H, W, C.c_float(maxD), C.c_void_p(out.ctypes.data))
+    return out
+
+
+def exp_neg(t):
+    L = lib(); L.orc_exp_neg.restype = C.c_float
+    return L.orc_exp_neg(C.c_float(t))
+
+
 def _f(a, n=None):
     a = np.ascontiguousarray(a, np.float32)
     if n is not None:

@@ -117,3 +117,18 @@ def test_trackers_sharing_the_gpu_are_independent_and_exact(torch_cuda, orc, syn
     [t.start() for t in ths]; [t.join() for t in ths]
     for t, R, ci, cr in outs:
         assert np.array_equal(t, to_) and np.array_equal(R, Ro) and ci == res.lastICPCount and cr == res.lastRGBCount
+
+
+@pytest.mark.parametrize("camname", ["vga", "kitti"])
+def test_depth_prefilter_bit_exact(torch_cuda, orc, synth, camname):
+    """N2: bilateral depth filter + metricise (depth_bilateral.frag:31-75, depth_metric.frag:29-39), the step before initICP(depth)."""
+    from densemonoslam_b200.odometry import filterDepth, metriciseDepth
+    cam = synth.CAM_VGA if camname == "vga" else synth.CAM_KITTI
+    scene = synth.street_scene(5) if camname == "kitti" else None
+    model, live, T = synth.frame_pair(cam, seed=31, scene=scene, max_depth=60.0, depth_noise=0.01)
+    raw = live["depth"].copy()
+    raw[::37, ::29] = 120     # below the 300 mm validity floor
+    maxD = 8.0 if camname == "kitti" else 3.5
+    d = to_dev(torch_cuda, raw)
+    assert np.array_equal(filterDepth(d, maxD).cpu().numpy(), orc.depth_bilateral(raw, maxD))
+    assert_f32_equal(metriciseDepth(d, maxD).cpu().numpy(), orc.depth_metric(raw, maxD), "metric depth")

@@ -140,3 +140,19 @@ def test_guard_rejects_large_translation(orc, synth):
     model, live, T = synth.frame_pair(cam, seed=3, tvec=(0.9, 0.0, 0.0), rvec=(0, 0, 0))
     t, R, res, _ = _track(orc, cam, model, live, (False, 10.0, True, False, False, False))
     assert np.linalg.norm(t) <= 0.3 + 1e-6
+
+
+def test_depth_prefilter_oracle(orc):
+    # depth_bilateral.frag:33-36: < 300 or > maxD*1000 -> 0; a constant patch is a fixed point; exp_neg accuracy
+    import math
+    d = np.full((40, 50), 1500, np.uint16); d[5, 5] = 100; d[10, 10] = 0; d[20, 20] = 5000
+    f = orc.depth_bilateral(d, 3.0)
+    assert f[5, 5] == 0 and f[10, 10] == 0 and f[20, 20] == 0 and f[0, 0] == 1500 and f[30, 30] == 1500
+    m = orc.depth_metric(d, 3.0)
+    assert m[0, 0] == np.float32(1.5) and m[5, 5] == 0 and m[20, 20] == 0
+    for t in (0.0, 0.3, 1.0, 7.7, 40.0):
+        assert abs(orc.exp_neg(t) - math.exp(-t)) <= 1e-5 * math.exp(-t)
+    rng = np.random.RandomState(0)
+    noisy = (1500 + rng.randint(-20, 21, size=(40, 50))).astype(np.uint16)
+    g = orc.depth_bilateral(noisy, 3.0).astype(int)
+    assert np.abs(g - 1500).mean() < np.abs(noisy.astype(int) - 1500).mean()   # it smooths
