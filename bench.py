@@ -185,9 +185,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=6, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--pipeline", type=int, default=8, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 1024)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -253,7 +255,11 @@ def main():
         hs, ss = [], []
         for k in range(depth):
             h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
-            h.set_grid(args.grid if args.grid else (0 if depth == 1 else sms // depth))
+            threads = args.threads if depth > 1 else 0  # a tracker that owns the GPU keeps one 1024-thread block per SM
+            if threads:
+                h.set_block(threads)
+            per_sm = max(1, 1024 // threads) if threads else 1
+            h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // depth))
             h.set_timing(True)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss
@@ -335,7 +341,9 @@ def main():
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
     depth = max(1, args.pipeline)
-    config["pipeline"] = (f"{depth} trackers share the GPU ({sms // depth} SMs each, own stream); frame f runs on tracker f % {depth}"
+    _thr = args.threads if args.threads else 1024
+    _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // depth
+    config["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
                           if depth > 1 else "single tracker, frames strictly one after another")
     pipe = make_pipe(depth)
     ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
@@ -344,6 +352,9 @@ def main():
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
     roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, depth)
 
+    if args.quick:
+        print(json.dumps({"value": value, "roofline": roofline, "config": config, "clocks": clocks}))
+        return
     e2e_steps = min(args.steps, 300)
     ms_e2e, _, _, _, _, _ = timed(pipe, e2e_steps, min(args.warmup, 5), True)
     e2e_value = world * e2e_steps / (ms_e2e * 1e-3)

@@ -54,8 +54,9 @@ struct TrackParams {
 static const int MAX_DBG = 1024;
 
 void threshold_equiv(float distThres, float angleThres, float* dist2Max, float* sine2Lim);
-int track_max_grid(int device, int* block_threads);  // co-resident CTAs for the cooperative launch
-cudaError_t launch_track(const TrackParams& p, int grid, cudaStream_t s);
+int track_block_threads_max();
+int track_max_grid(int device, int tpb);  // co-resident CTAs of tpb threads for the cooperative launch
+cudaError_t launch_track(const TrackParams& p, int grid, int tpb, cudaStream_t s);
 
 // single-step operators (regular launches + finalize)
 struct StepOut { float vals[28]; long long count, count2, sigma; int bad; int pad; };

@@ -32,6 +32,7 @@ struct dms_odom {
   // pinned host mirror of Ctrl / StepOut
   Ctrl* h_ctrl; StepOut* h_step;
   int grid, grid_max;    // CTAs of the cooperative tracking kernel in use / co-resident maximum
+  int tpb;               // threads per CTA of the tracking kernel
   int timing, tracing;
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
@@ -182,8 +183,12 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dms_odom_destroy(h); return (int)e; }
-  int tpb = 0;
-  h->grid = track_max_grid(device, &tpb);
+  h->tpb = track_block_threads_max();
+  if (const char* g = getenv("DMS_TRACK_THREADS")) {  // tuning knob: smaller CTAs (several co-resident per SM)
+    const int v = atoi(g);
+    if (v >= 64 && v <= h->tpb && (v & 31) == 0) h->tpb = v;
+  }
+  h->grid = track_max_grid(device, h->tpb);
   if (h->grid <= 0) { dms_odom_destroy(h); return DMS_ERR_DEVICE; }
   h->grid_max = h->grid;
   if (const char* g = getenv("DMS_TRACK_GRID")) {  // tuning knob: fewer co-resident CTAs than the maximum
@@ -214,6 +219,17 @@ int dms_odom_destroy(dms_odom* h) {
 int dms_odom_set_grid(dms_odom* h, int n_ctas) {
   if (!h || n_ctas < 0) return DMS_ERR_INVALID;
   h->grid = (n_ctas == 0 || n_ctas > h->grid_max) ? h->grid_max : (n_ctas < 2 ? 2 : n_ctas);
+  return DMS_OK;
+}
+int dms_odom_set_block(dms_odom* h, int threads) {
+  if (!h || threads < 0) return DMS_ERR_INVALID;
+  const int tpb = threads == 0 ? track_block_threads_max() : threads;
+  cudaSetDevice(h->device);
+  const int g = track_max_grid(h->device, tpb);
+  if (g <= 0) return DMS_ERR_INVALID;
+  const bool all = h->grid == h->grid_max;
+  h->tpb = tpb; h->grid_max = g;
+  if (all || h->grid > g) h->grid = g;
   return DMS_OK;
 }
 int dms_odom_set_timing(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->timing = enabled ? 1 : 0; return DMS_OK; }
@@ -348,7 +364,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = h->timing;
   P.dbg = h->timing ? h->dbg : nullptr;
   if (h->timing) { CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s)); CK(cudaEventRecord(h->ev0, s)); }
-  cudaError_t e = launch_track(P, h->grid, s);
+  cudaError_t e = launch_track(P, h->grid, h->tpb, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
   if (h->timing) CK(cudaEventRecord(h->ev1, s));
   CK(cudaMemcpyAsync(h->h_ctrl, h->ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
@@ -549,6 +565,7 @@ int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t*
     case DMS_BUF_DIDY: p = L.dIdy; pb = L.pitch_s16; e = 2; break;
     case DMS_BUF_DEPTH_TMP: p = L.depth_tmp; pb = L.pitch_u16; e = 2; break;
     case DMS_BUF_CORRES: p = L.corr; pb = L.pitch_corr; e = 8; break;
+    case DMS_BUF_NEXT_DEPTH_MASKED: p = L.nextDepthMasked; pb = L.pitch_f32; break;
     default: return fail(h, DMS_ERR_INVALID, "get_buffer: unknown buffer");
   }
   if (d_ptr) *d_ptr = p;

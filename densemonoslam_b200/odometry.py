@@ -13,10 +13,10 @@ import numpy as np
 from . import _lib
 
 BUF = {"vmap_curr": 0, "nmap_curr": 1, "vmap_g_prev": 2, "nmap_g_prev": 3, "lastDepth": 4, "nextDepth": 5, "lastImage": 6,
-       "nextImage": 7, "lastNextImage": 8, "dIdx": 9, "dIdy": 10, "depth_tmp": 11, "corr": 12}
+       "nextImage": 7, "lastNextImage": 8, "dIdx": 9, "dIdy": 10, "depth_tmp": 11, "corr": 12, "nextDepthMasked": 13}
 CORR_DTYPE = np.dtype([("u0", "<i2"), ("v0", "<i2"), ("diff", "<i2"), ("valid", "u1"), ("pad", "u1")])
 _BUF_DT = {0: np.float32, 1: np.float32, 2: np.float32, 3: np.float32, 4: np.float32, 5: np.float32, 6: np.uint8, 7: np.uint8,
-           8: np.uint8, 9: np.int16, 10: np.int16, 11: np.uint16, 12: CORR_DTYPE}
+           8: np.uint8, 9: np.int16, 10: np.int16, 11: np.uint16, 12: CORR_DTYPE, 13: np.float32}
 
 # default angleThresh of the reference constructor: sin(20.f * 3.14159254f / 180.f)  (RO.h:36)
 DEFAULT_ANGLE_THRESH = float(np.sin(np.float32(20.0) * np.float32(3.14159254) / np.float32(180.0)))
@@ -235,6 +235,10 @@ class RGBDOdometry:
 
     def set_grid(self, n_ctas=0):
         self._ck(self._L.dms_odom_set_grid(self._h, int(n_ctas)), "set_grid")
+
+    def set_block(self, threads=0):
+        """Threads per block of the tracking kernel (0 = 1024); call before set_grid."""
+        self._ck(self._L.dms_odom_set_block(self._h, int(threads)), "set_block")
 
     def set_timing(self, enabled=True):
         self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")

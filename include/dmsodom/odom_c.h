@@ -74,6 +74,10 @@ const char* dms_odom_last_error(const dms_odom* h);
  * concurrently on one GPU, each on its own stream: the barrier / solve latency of one overlaps the pixel phases of
  * the others.  Results do not depend on the limit (the reduction is order-free). */
 int dms_odom_set_grid(dms_odom* h, int n_ctas);
+/* Threads per thread block of the tracking kernel (multiple of 32 in [64, 1024]; 0 = 1024).  With 512 or fewer, two or
+ * more blocks (of different handles) are resident per SM, so one tracker's pixel phases fill the issue slots another
+ * leaves idle at its barriers.  Resets the grid limit to "all" when it no longer fits.  Results do not depend on it. */
+int dms_odom_set_block(dms_odom* h, int threads);
 int dms_odom_set_timing(dms_odom* h, int enabled);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
 
@@ -132,7 +136,8 @@ enum dms_buffer {
   DMS_BUF_VMAP_CURR = 0, DMS_BUF_NMAP_CURR = 1, DMS_BUF_VMAP_G_PREV = 2, DMS_BUF_NMAP_G_PREV = 3,
   DMS_BUF_LAST_DEPTH = 4, DMS_BUF_NEXT_DEPTH = 5, DMS_BUF_LAST_IMAGE = 6, DMS_BUF_NEXT_IMAGE = 7,
   DMS_BUF_LAST_NEXT_IMAGE = 8, DMS_BUF_DIDX = 9, DMS_BUF_DIDY = 10, DMS_BUF_DEPTH_TMP = 11,
-  DMS_BUF_CORRES = 12 /* 8-byte records {i16 u0, i16 v0, i16 diff, u8 valid, u8 0}: compact DataTerm, types.cuh:76-82 */
+  DMS_BUF_CORRES = 12, /* 8-byte records {i16 u0, i16 v0, i16 diff, u8 valid, u8 0}: compact DataTerm, types.cuh:76-82 */
+  DMS_BUF_NEXT_DEPTH_MASKED = 13 /* nextDepth with NaN where the iteration-invariant tests of reduce.cu:777-801 fail */
 };
 int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t* pitch_bytes, int* rows, int* cols,
                         int* elem_bytes);

@@ -32,8 +32,8 @@
 //   * float -> int pixel rounding = CUDA __float2int_rn (ties to even, NaN -> 0,
 //     saturating).
 //   * reductions: "canonical tree" -- every image row is cut into segments of 32
-//     consecutive pixels; a pixel's products row[i]*row[j] are fp32 multiplies, the 32
-//     pixels of a segment are added sequentially (pixel 0 first) in fp32, and segment
+//     consecutive pixels; product (i, j) is accumulated over the 32 pixels of a segment
+//     in order (pixel 0 first) as s = fmaf(row[i], row[j], s) in fp32, and segment
 //     sums are accumulated EXACTLY in a 2x64-bit fixed-point accumulator, so the result
 //     does not depend on how segments are scheduled.  Counts are integers.
 // =====================================================================================
@@ -114,9 +114,10 @@ struct Exact {
 static const int SEGW = 32;     // pixels per segment: 32 consecutive pixels of one image row (one GPU warp)
 
 // Generic canonical reduction.  pix(x, y, row[NR]) fills the Jacobian row of one pixel and returns true
-// when the pixel contributes.  Per pixel the products row[i]*row[j] (i<=j) are formed (fp32 multiply);
-// within a segment they are added sequentially, pixel 0 first (fp32); segment sums are accumulated
-// exactly.  The count of contributing pixels is an integer.
+// when the pixel contributes.  Within a segment product (i, j), i <= j, is accumulated over the pixels in
+// order, pixel 0 first, as s = fma(row[i], row[j], s) in fp32 (the reference's own per-thread accumulation
+// `sum.add(getProducts(i))`, reduce.cu:350-356, contracts to the same FFMA under nvcc's default -fmad);
+// segment sums are accumulated exactly.  The count of contributing pixels is an integer.
 template <int NR, class PixFn>
 static void canonical_products(int rows, int cols, PixFn pix, float* out_products, int64_t* out_count) {
   const int NP = NR * (NR + 1) / 2;
@@ -141,7 +142,7 @@ static void canonical_products(int rows, int cols, PixFn pix, float* out_product
           ++lcount;
           int k = 0;
           for (int i = 0; i < NR; ++i)
-            for (int j = i; j < NR; ++j, ++k) segacc[k] = segacc[k] + row[i] * row[j];
+            for (int j = i; j < NR; ++j, ++k) segacc[k] = fmaf(row[i], row[j], segacc[k]);
         }
       }
       for (int k = 0; k < NP; ++k) loc[k].addf(segacc[k]);
