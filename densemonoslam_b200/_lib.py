@@ -35,7 +35,27 @@ class DmsStepSums(C.Structure):
                 ("bad", C.c_int32), ("reserved2", C.c_int32)]
 
 
-# every symbol declared in include/dmsodom/odom_c.h (tests check the header against this list)
+class DmsModelView(C.Structure):
+    _fields_ = [("d_vertex", C.c_void_p), ("d_normal", C.c_void_p), ("d_image", C.c_void_p)]
+
+
+class DmsFrontendOptions(C.Structure):
+    _fields_ = [("depthCutoff", C.c_float), ("icpWeight", C.c_float), ("rgbOnly", C.c_int), ("pyramid", C.c_int), ("fastOdom", C.c_int),
+                ("so3", C.c_int), ("frameToFrameRGB", C.c_int), ("reloc", C.c_int), ("closeLoops", C.c_int), ("hybridTracking", C.c_int),
+                ("weightMultiplier", C.c_float)]
+
+
+class DmsFrontendResult(C.Structure):
+    _fields_ = [("tick", C.c_int), ("tracked", C.c_int), ("pose", C.c_float * 16), ("shouldFillIn", C.c_int), ("denseFraction", C.c_float),
+                ("trackingOk", C.c_int), ("lost", C.c_int), ("trackingCount", C.c_int), ("lastFrameRecovery", C.c_int),
+                ("weighting", C.c_float), ("frameToModel", DmsResult), ("loopChecked", C.c_int), ("loopAccepted", C.c_int),
+                ("loopPose", C.c_float * 16), ("loopCovDiag", C.c_double * 6), ("modelToModel", DmsResult)]
+
+
+# int (*dms_predict_fn)(void* user, const float pose[16], int kind, int tick, void* stream, dms_model_view* out)
+PREDICT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p, C.POINTER(DmsModelView))
+
+# every symbol declared in include/dmsodom/*.h (tests check the headers against this list)
 _P = C.c_void_p
 _F3 = C.POINTER(C.c_float)
 SIGNATURES = {
@@ -78,6 +98,18 @@ SIGNATURES = {
     "dms_depth_metric": (C.c_int, [_P, C.c_size_t, C.c_int, C.c_int, C.c_float, _P, C.c_size_t, _P]),
     "dms_icp_step_noalloc": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                        _F3, _F3, _F3, _F3, C.c_float, C.c_float, _P, _P]),
+    "dms_frontend_default_options": (None, [C.POINTER(DmsFrontendOptions)]),
+    "dms_frontend_create": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + [C.POINTER(DmsFrontendOptions)]),
+    "dms_frontend_destroy": (C.c_int, [_P]),
+    "dms_frontend_set_predictor": (C.c_int, [_P, PREDICT_FN, _P]),
+    "dms_frontend_process": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_size_t, _F3, C.POINTER(DmsFrontendResult), _P]),
+    "dms_frontend_get_tracker": (C.c_int, [_P, C.c_int, C.POINTER(_P)]),
+    "dms_frontend_get_filtered_depth": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),
+    "dms_frontend_get_fill_in": (C.c_int, [_P, C.POINTER(DmsModelView)]),
+    "dms_frontend_set_state": (C.c_int, [_P, C.c_int, C.c_int]),
+    "dms_fill_in": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int] + [C.c_float] * 4 + [C.c_int, C.c_int, _P, _P, _P, _P]),
+    "dms_dense_fraction": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, C.POINTER(C.c_float), _P]),
+    "dms_velocity_weighting": (C.c_float, [_F3, _F3, C.c_float]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

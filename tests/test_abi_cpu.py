@@ -1,4 +1,4 @@
-"""The C-ABI library loads and exports every symbol include/dmsodom/odom_c.h declares (no GPU needed)."""
+"""The C-ABI library loads and exports every symbol include/dmsodom/*_c.h declares (no GPU needed)."""
 import ctypes
 import os
 import re
@@ -8,13 +8,17 @@ import pytest
 
 from conftest import ROOT
 
-HEADER = os.path.join(ROOT, "include", "dmsodom", "odom_c.h")
+HEADERS = [os.path.join(ROOT, "include", "dmsodom", n) for n in ("odom_c.h", "frontend_c.h")]
 
 
 def declared_symbols():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(dms_[a-z0-9_]+)\s*\(", src)))
+    names = set()
+    for h in HEADERS:
+        src = open(h).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        src = re.sub(r"typedef[^;]*\(\s*\*\s*\w+\s*\)[^;]*;", "", src)  # function-pointer typedefs are not entry points
+        names |= set(re.findall(r"\b(dms_[a-z0-9_]+)\s*\(", src))
+    return sorted(names)
 
 
 def test_header_symbols_are_exported_and_bound():
@@ -24,7 +28,7 @@ def test_header_symbols_are_exported_and_bound():
     assert os.path.exists(_lib.LIB_PATH), "build densemonoslam_b200/lib/libdmsodom.so first (__graft_entry__.build())"
     lib = ctypes.CDLL(_lib.LIB_PATH)
     for n in names:
-        assert hasattr(lib, n), f"{n} declared in odom_c.h but not exported"
+        assert hasattr(lib, n), f"{n} declared in include/dmsodom but not exported"
         assert n in _lib.SIGNATURES, f"{n} has no ctypes signature in densemonoslam_b200/_lib.py"
     assert sorted(_lib.SIGNATURES) == names
     assert b"dmsodom" in _lib.load().dms_version()

@@ -156,3 +156,31 @@ def test_depth_prefilter_oracle(orc):
     noisy = (1500 + rng.randint(-20, 21, size=(40, 50))).astype(np.uint16)
     g = orc.depth_bilateral(noisy, 3.0).astype(int)
     assert np.abs(g - 1500).mean() < np.abs(noisy.astype(int) - 1500).mean()   # it smooths
+
+
+def test_frontend_restatement_pieces():
+    """oracle/frontend_ref.py (N1): FillIn selection rules, denseEnough sampling, rodrigues2, velocity weighting."""
+    from oracle import frontend_ref as ref
+    H, W = 40, 60
+    mv = np.zeros((H, W, 4), np.float32); mn = np.zeros((H, W, 4), np.float32); mi = np.zeros((H, W, 4), np.uint8)
+    mv[:20, :, :3] = (0.1, 0.2, 1.5); mn[:20, :, :3] = (0.0, 0.0, -1.0); mi[:20] = (10, 20, 30, 255)
+    depth = np.full((H, W), 2000, np.uint16); live = np.full((H, W, 4), 77, np.uint8)
+    cam = (29.5, 19.5, 50.0, 50.0)
+    ov, on, oi = ref.fill_in(mv, mn, mi, depth, live, cam)
+    assert np.array_equal(ov[:20], mv[:20]) and np.array_equal(on[:20], mn[:20]) and np.array_equal(oi[:20], mi[:20])
+    assert np.all(ov[20:, :, 2] == np.float32(2.0)) and np.all(oi[20:] == 77)
+    assert ov[30, 40, 0] == (np.float32(40) - np.float32(29.5)) * np.float32(2.0) * (np.float32(1) / np.float32(50))
+    assert np.allclose(on[25, 10, :3], (0, 0, 1), atol=1e-6)   # fronto-parallel plane: cross(dx, dy) = +z
+    ov2, _, oi2 = ref.fill_in(mv, mn, mi, depth, live, cam, pass_geom=True, pass_img=True)
+    assert np.all(ov2[..., 2] == np.float32(2.0)) and np.all(oi2 == 77)
+    assert ref.dense_fraction(mi) <= np.float32(0.5) and ref.dense_fraction(live) == np.float32(1.0)
+    rv = np.array([0.01, -0.02, 0.015])
+    from densemonoslam_b200 import synth
+    T = synth.pose_from(rv, (0, 0, 0))
+    assert np.allclose(ref.rodrigues2(T[:3, :3]), rv, atol=1e-6)
+    a = synth.pose_from((0.1, 0.2, 0.3), (1, 2, 3)).astype(np.float32)
+    assert ref.velocity_weighting(a, a, 2.0) == 2.0                      # no motion: full weight
+    b = (a @ synth.pose_from((0, 0, 0), (0.005, 0, 0))).astype(np.float32)
+    assert abs(ref.velocity_weighting(b, a) - 0.5) < 1e-3               # half of `largest`
+    c = (a @ synth.pose_from((0.2, 0, 0), (0, 0, 0))).astype(np.float32)
+    assert ref.velocity_weighting(c, a) == 0.5                           # clamped at minWeight
