@@ -110,6 +110,13 @@ SIGNATURES = {
     "dms_fill_in": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int] + [C.c_float] * 4 + [C.c_int, C.c_int, _P, _P, _P, _P]),
     "dms_dense_fraction": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, C.POINTER(C.c_float), _P]),
     "dms_velocity_weighting": (C.c_float, [_F3, _F3, C.c_float]),
+    "dms_nid_create": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "dms_nid_destroy": (C.c_int, [_P]),
+    "dms_nid_set_keyframe": (C.c_int, [_P, _P, _P, _P, _P, C.c_float, _P]),
+    "dms_nid_score": (C.c_int, [_P, _P, C.c_float, C.c_float, _F3, _F3, _F3, _P]),
+    "dms_nid_get_histogram": (C.c_int, [_P, C.c_int, _P, C.c_size_t, _P]),
+    "dms_nid_image": (C.c_int, [_P, _P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, _P, _P, _F3, _P]),
+    "dms_nid_depth": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_float, _P, _P, _F3, _P]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

@@ -124,6 +124,21 @@ void ref_so3_step(const uint8_t* lastImage, const uint8_t* nextImage, const floa
   so3Step(li, ni, m33(H), m33(kinv), m33(krlr), sum, out, A, b, residual, threads, blocks);
 }
 
+// computeNIDImg (cf.cu:1513-1650) / computeNIDDepth (cf.cu:1794-1915): the reference's own histogram kernels and host entropy loops
+float ref_nid_img(const uint8_t* ik, const uint8_t* iko, const float* dk, const float* dko, const uint8_t* ic, int rows, int cols, int nb) {
+  DeviceArray2D<unsigned char> a, b, c; DeviceArray2D<float> d, e;
+  up2d(a, ik, rows, cols); up2d(b, iko, rows, cols); up2d(c, ic, rows, cols); up2d(d, dk, rows, cols); up2d(e, dko, rows, cols);
+  float nid = 0.f;
+  computeNIDImg(a, b, d, e, c, nid, nb, false);
+  return nid;
+}
+float ref_nid_depth(const float* dk, const float* dko, const float* dc, int rows, int cols, int nb, float max_depth_mm) {
+  DeviceArray2D<float> d, e, c;
+  up2d(d, dk, rows, cols); up2d(e, dko, rows, cols); up2d(c, dc, rows, cols);
+  float nid = 0.f;
+  computeNIDDepth(d, e, c, nid, nb, max_depth_mm, false);
+  return nid;
+}
 }  // extern "C"
 
 // =====================================================================================================

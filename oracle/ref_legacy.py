@@ -49,6 +49,19 @@ def pyrdown_f32_gauss(src):
     lib().ref_pyrdown_f32_gauss(_p(_f(src)), H, W, _p(out)); return out
 
 
+def nid_img(img_kf, img_kf_old, dmap_kf, dmap_kf_old, img_curr, nb):
+    H, W = img_curr.shape
+    f = lib().ref_nid_img; f.restype = C.c_float
+    return float(f(_p(np.ascontiguousarray(img_kf)), _p(np.ascontiguousarray(img_kf_old)), _p(_f(dmap_kf)), _p(_f(dmap_kf_old)),
+                   _p(np.ascontiguousarray(img_curr)), H, W, int(nb)))
+
+
+def nid_depth(dmap_kf, dmap_kf_old, dmap_curr, nb, max_depth_mm):
+    H, W = dmap_curr.shape
+    f = lib().ref_nid_depth; f.restype = C.c_float
+    return float(f(_p(_f(dmap_kf)), _p(_f(dmap_kf_old)), _p(_f(dmap_curr)), H, W, int(nb), C.c_float(max_depth_mm)))
+
+
 def pyrdown_u16(src):
     H, W = src.shape; out = np.empty((H // 2, W // 2), np.uint16)
     lib().ref_pyrdown_u16(_p(np.ascontiguousarray(src)), H, W, _p(out)); return out

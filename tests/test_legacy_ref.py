@@ -71,3 +71,32 @@ def test_full_track_against_reference_loop(orc, synth, ref):
     assert abs(res.lastICPCount - r.out[1]) <= 2e-3 * r.out[1], rep
     assert abs(res.lastRGBCount - r.out[3]) <= 5e-3 * max(r.out[3], 1), rep
     assert np.max(np.abs(tr - T[:3, 3])) < 5e-3
+
+
+@pytest.mark.parametrize("nb_img,nb_depth", [(64, 500), (32, 100)])
+def test_nid_restatement_against_reference_kernels(orc, synth, ref, nb_img, nb_depth):
+    """N4: oracle/nid_ref.py vs the reference's computeNIDImg / computeNIDDepth (cf.cu:1513-1650, 1794-1915) on the same
+    pyramids, in-range depths only (the reference's histogram has no bounds check)."""
+    from oracle import nid_ref
+    cam = synth.scaled_camera(synth.CAM_VGA, 2)
+    scene = synth.room_scene(21)
+    kf = synth.render(scene, cam, np.eye(4), seed=1, max_depth=50.0)
+    old = synth.render(scene, cam, synth.pose_from((0.01, 0.0, 0.0), (0.03, 0.0, 0.0)), seed=2, max_depth=50.0)
+    live = synth.render(scene, cam, synth.pose_from((0.02, -0.01, 0.0), (0.05, 0.02, 0.01)), seed=3, max_depth=50.0)
+    cutoff = 3.5
+    ik, dk = nid_ref.keyframe_pyramids(kf["vmap4"], kf["rgba"], cutoff, 1)
+    iko, dko = nid_ref.keyframe_pyramids(old["vmap4"], old["rgba"], cutoff, 1)
+    ic, dc = nid_ref.keyframe_pyramids(live["vmap4"], live["rgba"], cutoff, 1)
+    n = ic.size
+    max_mm = 6000.0   # every finite depth (< 3.5 m) stays inside the histogram
+    r_img = ref.nid_img(ik, iko, dk, dko, ic, nb_img)
+    r_dep = ref.nid_depth(dk, dko, dc, nb_depth, max_mm)
+    o_img = float(nid_ref.nid_from_hist(nid_ref.hist_img(ik, iko, dk, dko, ic, nb_img), n))
+    o_dep = float(nid_ref.nid_from_hist(nid_ref.hist_depth(dk, dko, dc, nb_depth, max_mm), n))
+    out_dir = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out_dir, exist_ok=True)
+    json.dump({"nid_img": {"reference": r_img, "oracle": o_img}, "nid_depth": {"reference": r_dep, "oracle": o_dep}},
+              open(os.path.join(out_dir, f"legacy_nid_{nb_img}_{nb_depth}.json"), "w"), indent=1)
+    # same integer histograms; host entropy loops in fp32 with glibc log2f on both sides
+    assert abs(r_img - o_img) <= 2e-6 * abs(r_img), (r_img, o_img)
+    assert abs(r_dep - o_dep) <= 2e-6 * abs(r_dep), (r_dep, o_dep)

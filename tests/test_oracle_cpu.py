@@ -184,3 +184,24 @@ def test_frontend_restatement_pieces():
     assert abs(ref.velocity_weighting(b, a) - 0.5) < 1e-3               # half of `largest`
     c = (a @ synth.pose_from((0.2, 0, 0), (0, 0, 0))).astype(np.float32)
     assert ref.velocity_weighting(c, a) == 0.5                           # clamped at minWeight
+
+
+def test_nid_restatement_pieces():
+    """oracle/nid_ref.py (N4): NaN-comparison quirk of the key-frame pick, bin rules, entropy identities."""
+    from oracle import nid_ref as nr
+    nan = np.float32(np.nan)
+    dk = np.array([[1.0, nan, 2.0, nan]], np.float32); dko = np.array([[2.0, 1.0, nan, nan]], np.float32)
+    assert nr.pick_active(dk, dko).tolist() == [[True, False, False, False]]
+    ik = np.array([[10, 20, 30, 40]], np.uint8); iko = np.array([[200, 210, 220, 230]], np.uint8); ic = np.array([[0, 255, 128, 64]], np.uint8)
+    h = nr.hist_img(ik, iko, dk, dko, ic, 64)
+    assert h.sum() == 4 and h[0, 10 // 4] == 1 and h[255 // 4, 210 // 4] == 1 and h[128 // 4, 220 // 4] == 1
+    hd = nr.hist_depth(dk, dko, np.array([[1.0, nan, 2.9, 5.0]], np.float32), 500, 3000.0)
+    assert hd[int(1000 / 6), int(1000 / 6)] == 1      # 1 m vs 1 m
+    assert hd[0, int(1000 / 6)] == 1                  # NaN live depth -> bin 0 (device float->int of NaN)
+    assert hd.sum() == 3                              # 5 m live depth falls outside the histogram: dropped
+    rng = np.random.RandomState(0)
+    a = rng.randint(0, 256, (60, 80)).astype(np.uint8)
+    z = np.ones((60, 80), np.float32)
+    same = nr.nid_from_hist(nr.hist_img(a, a, z, z, a, 64), a.size)
+    indep = nr.nid_from_hist(nr.hist_img(a, a, z, z, rng.randint(0, 256, (60, 80)).astype(np.uint8), 64), a.size)
+    assert abs(float(same)) < 1e-5 and 0.7 < float(indep) <= 1.0   # identical images: distance 0; independent: near 1
