@@ -293,13 +293,17 @@ def main():
         sampler = ClockSampler(local_rank)
         sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        stats = [{"k": [], "it": [], "so3": [], "last": None} for _ in range(depth)]
+        stats = [{"k": [], "it": [], "so3": [], "last": None, "lat": [], "phase": []} for _ in range(depth)]
 
         def work(k):
             torch.cuda.set_device(local_rank)
             for i in range(k, steps, depth):
+                t_host = time.perf_counter()
                 out = one_frame(hs[k], ss[k], i, host)
-                stats[k]["k"].append(hs[k].timing()["track"]); stats[k]["it"].append(list(hs[k].iters)); stats[k]["so3"].append(hs[k].so3_iters)
+                stats[k]["lat"].append((time.perf_counter() - t_host) * 1e3)   # host-visible latency of one frame (result in hand)
+                tm = hs[k].timing()
+                stats[k]["k"].append(tm["track"]); stats[k]["it"].append(list(hs[k].iters)); stats[k]["so3"].append(hs[k].so3_iters)
+                stats[k]["phase"].append(tm)
                 if i == steps - 1:
                     stats[k]["last"] = out
         ev0.record()
@@ -321,6 +325,8 @@ def main():
         iters_seen = [x for s_ in stats for x in s_["it"]]
         so3_seen = [x for s_ in stats for x in s_["so3"]]
         last = [s_["last"] for s_ in stats if s_["last"] is not None][0]
+        timed.latencies = [x for s_ in stats for x in s_["lat"]]
+        timed.phases = [x for s_ in stats for x in s_["phase"]]
         return ms, ktimes, iters_seen, so3_seen, clocks, last
 
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -381,7 +387,14 @@ def main():
         pipe1 = make_pipe(1)
         ms1, k1, it1, s31, _, _ = timed(pipe1, min(args.steps, 300), args.warmup, False)
         n1 = min(args.steps, 300)
+        lat = np.sort(np.array(timed.latencies))
+        ph = {k: float(np.mean([p_[k] for p_ in timed.phases])) * 1e3 for k in timed.phases[0]}
+        gn_its = max(1, int(np.mean([sum(it) for it in it1])))
         out["single_tracker"] = {"value": n1 / (ms1 * 1e-3), "unit": "frames/s", "latency_ms_per_frame": ms1 / n1,
+                                 "host_latency_ms": {"p50": float(lat[len(lat) // 2]), "p99": float(lat[min(len(lat) - 1, int(len(lat) * 0.99))]),
+                                                     "max": float(lat[-1]), "frames": int(len(lat))},
+                                 "track_us": ph.get("track"), "phase_us": ph,
+                                 "us_per_gn_iteration": (ph.get("icpStep", 0.0) + ph.get("rgbStep", 0.0) + ph.get("computeRgbResidual", 0.0)) / gn_its,
                                  "roofline": roofline_of(ms1, n1, k1, it1, s31, 1)}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -52,6 +52,12 @@ class DmsFrontendResult(C.Structure):
                 ("loopPose", C.c_float * 16), ("loopCovDiag", C.c_double * 6), ("modelToModel", DmsResult)]
 
 
+class DmsSplatParams(C.Structure):
+    _fields_ = [("t_inv", C.c_float * 16), ("cx", C.c_float), ("cy", C.c_float), ("fx", C.c_float), ("fy", C.c_float), ("rows", C.c_int),
+                ("cols", C.c_int), ("maxDepth", C.c_float), ("confThreshold", C.c_float), ("time", C.c_int), ("timeIdx", C.c_int),
+                ("maxTime", C.c_int), ("timeDelta", C.c_int), ("active", C.c_int)]
+
+
 # int (*dms_predict_fn)(void* user, const float pose[16], int kind, int tick, void* stream, dms_model_view* out)
 PREDICT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p, C.POINTER(DmsModelView))
 
@@ -117,6 +123,8 @@ SIGNATURES = {
     "dms_nid_get_histogram": (C.c_int, [_P, C.c_int, _P, C.c_size_t, _P]),
     "dms_nid_image": (C.c_int, [_P, _P, _P, _P, _P, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, _P, _P, _F3, _P]),
     "dms_nid_depth": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_float, _P, _P, _F3, _P]),
+    "dms_splat_predict": (C.c_int, [_P, C.c_int, C.POINTER(DmsSplatParams), _P, _P, _P, _P, _P, _P]),
+    "dms_splat_invert_pose": (C.c_int, [_F3, _F3]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

@@ -205,3 +205,33 @@ def test_nid_restatement_pieces():
     same = nr.nid_from_hist(nr.hist_img(a, a, z, z, a, 64), a.size)
     indep = nr.nid_from_hist(nr.hist_img(a, a, z, z, rng.randint(0, 256, (60, 80)).astype(np.uint8), 64), a.size)
     assert abs(float(same)) < 1e-5 and 0.7 < float(indep) <= 1.0   # identical images: distance 0; independent: near 1
+
+
+def test_splat_restatement_pieces():
+    """oracle/splat_ref.py (N3): disk footprint, depth order / draw-order ties, visibility rules of splat.vert:46-50."""
+    from oracle import splat_ref as sr
+    cam = (31.5, 23.5, 60.0, 60.0); rows, cols = 48, 64
+    def surfel(x, y, z, rad, col, conf=10.0, t=5.0, init=5.0, n=(0, 0, -1)):
+        s = np.zeros(15, np.float32); s[0:4] = (x, y, z, conf); s[4] = col; s[6] = init; s[8:11] = (t, -3, -3); s[11:14] = n; s[14] = rad
+        return s
+    I = np.eye(4, dtype=np.float32)
+    args = dict(t_inv=I, cam=cam, rows=rows, cols=cols, maxDepth=5.0, confThreshold=5.0, time=6, timeIdx=0, maxTime=6, timeDelta=200, active=1)
+    # one fronto-parallel surfel at 2 m with radius 0.1 m: a disk of radius 0.1 * 60 / 2 = 3 px around (31.5, 23.5)
+    img, ver, nor, tim = sr.predict(np.stack([surfel(0, 0, 2.0, 0.1, (200 << 16) + (100 << 8) + 50)]), **args)
+    yy, xx = np.nonzero(ver[..., 2] > 0)
+    r = np.hypot(xx + 0.5 - 31.5, yy + 0.5 - 23.5)
+    assert r.max() <= 3.0 + 1e-3 and len(r) == int((np.hypot(*np.meshgrid(np.arange(64) + 0.5 - 31.5, np.arange(48) + 0.5 - 23.5)) <= 3.0).sum())
+    assert img[23, 31].tolist() == [200, 100, 50, 255] and tim[23, 31] == 5 and ver[23, 31, 2] == np.float32(2.0) and ver[23, 31, 3] == 10.0
+    # nearer surfel wins; equal depth: the one drawn first wins
+    near = surfel(0, 0, 1.5, 0.02, 7); same_a = surfel(0.2, 0, 2.0, 0.05, 11); same_b = surfel(0.2, 0, 2.0, 0.05, 12)
+    img, ver, _, _ = sr.predict(np.stack([surfel(0, 0, 2.0, 0.1, 9), near, same_a, same_b]), **args)
+    assert img[23, 31, 2] == 7 and ver[23, 31, 2] == np.float32(1.5)
+    px = int(31.5 + 0.2 * 60 / 2.0)
+    assert img[23, px, 2] == 11
+    # visibility: low confidence, beyond maxDepth, stale (time - t > timeDelta), newer than maxTime, unseen (-3) in ACTIVE mode
+    for bad in (surfel(0, 0, 2, 0.1, 1, conf=1.0), surfel(0, 0, 6, 0.1, 1), surfel(0, 0, 2, 0.1, 1, t=7.0)):
+        assert not (sr.predict(np.stack([bad]), **args)[1][..., 2] > 0).any()
+    assert not (sr.predict(np.stack([surfel(0, 0, 2, 0.1, 1, t=1.0)]), **{**args, "timeDelta": 3})[1][..., 2] > 0).any()
+    unseen = surfel(0, 0, 2, 0.1, 1, t=-3.0)
+    assert not (sr.predict(np.stack([unseen]), **args)[1][..., 2] > 0).any()
+    assert (sr.predict(np.stack([unseen]), **{**args, "active": 0})[1][..., 2] > 0).any()   # INACTIVE keeps -3 surfels (splat.vert:46)
