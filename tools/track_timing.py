@@ -7,6 +7,7 @@ from densemonoslam_b200 import synth
 from densemonoslam_b200.odometry import RGBDOdometry
 
 name = sys.argv[1] if len(sys.argv) > 1 else "vga"
+icp_weight = float(sys.argv[2]) if len(sys.argv) > 2 else 10.0   # 100 = ICP only (RO.cpp:279)
 cam = {"vga": synth.CAM_VGA, "kitti": synth.CAM_KITTI, "1080p": synth.CAM_1080P, "small": synth.scaled_camera(synth.CAM_VGA, 4)}[name]
 model, live, T = synth.frame_pair(cam, seed=1234)
 dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
@@ -19,7 +20,7 @@ acc = {}
 N = 30
 for i in range(N + 5):
     g.initICPModel(mv, mn, 25.0, pose); g.initRGBModel(mi); g.initICP(ld, 25.0); g.initRGB(li)
-    g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
+    g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, icp_weight, True, False, True)
     if i >= 5:
         for k, v in g.timing().items():
             acc[k] = acc.get(k, 0.0) + v / N
