@@ -46,48 +46,62 @@ __device__ __forceinline__ float3 box4(float3 a, float3 b, float3 c, float3 d, b
   return n;
 }
 
-// One thread per 4x4 block of level-0 pixels: writes 16 L0, 4 L1 and 1 L2 outputs.
+// One thread per 2x2 block of level-0 pixels (= one level-1 pixel): writes 4 L0 and 1 L1 outputs; the level-2 pixel of a
+// 4x4 block is assembled from its four threads with shuffles.  A warp covers 16 x 2 level-1 pixels (lane = ly * 16 + lx),
+// so rows are read as 512 contiguous bytes and the level-0 planes are written as float2 pairs.
+__device__ __forceinline__ void store_plane3_pair(float* base, int pitch, int rows, int y, int x, float3 a, float3 b) {
+  *reinterpret_cast<float2*>(row_ptr(base, pitch, y) + x) = make_float2(a.x, b.x);
+  *reinterpret_cast<float2*>(row_ptr(base, pitch, y + rows) + x) = make_float2(a.y, b.y);
+  *reinterpret_cast<float2*>(row_ptr(base, pitch, y + 2 * rows) + x) = make_float2(a.z, b.z);
+}
+__device__ __forceinline__ float3 shfl3(float3 v, int src) {
+  return make_float3(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src));
+}
 template <bool TRANSFORM>
 __global__ void __launch_bounds__(128) k_maps_pyramid(const MapsPyrArgs a) {
-  const int bx = blockIdx.x * blockDim.x + threadIdx.x;
-  const int by = blockIdx.y * blockDim.y + threadIdx.y;
-  const int x0 = bx * 4, y0 = by * 4;
-  if (x0 >= a.cols[0] || y0 >= a.rows[0]) return;
-  float3 v1[4], n1[4];  // level-1 values (before transform) of the 2x2 sub-blocks
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int x1 = blockIdx.x * 32 + (warp & 1) * 16 + (lane & 15);   // level-1 pixel of this thread
+  const int y1 = blockIdx.y * 4 + (warp >> 1) * 2 + (lane >> 4);
+  const int x0 = x1 * 2, y0 = y1 * 2;
+  float3 v0[4], n0[4];
 #pragma unroll
-  for (int sy = 0; sy < 2; ++sy) {
+  for (int q = 0; q < 4; ++q) {
+    const int x = x0 + (q & 1), y = y0 + (q >> 1);
+    float3 v = make_float3(qnan(), qnan(), qnan()), n = v;
+    if (x < a.cols[0] && y < a.rows[0]) {
+      const float4 vs = __ldg(row_ptr(a.v4, a.pitch4, y) + x);
+      const float4 ns = __ldg(row_ptr(a.n4, a.pitch4, y) + x);
+      if (!(vs.z == 0)) { v = make_float3(vs.x, vs.y, vs.z); n = make_float3(ns.x, ns.y, ns.z); }
+      row_ptr(a.zdepth, a.pitch[0], y)[x] = (vs.z > a.zcut || vs.z <= 0) ? qnan() : vs.z;
+    }
+    v0[q] = v; n0[q] = n;
+  }
 #pragma unroll
-    for (int sx = 0; sx < 2; ++sx) {
-      float3 v0[4], n0[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int x = x0 + sx * 2 + (q & 1), y = y0 + sy * 2 + (q >> 1);
-        float3 v = make_float3(qnan(), qnan(), qnan()), n = v;
-        if (x < a.cols[0] && y < a.rows[0]) {
-          const float4 vs = __ldg(row_ptr(a.v4, a.pitch4, y) + x);
-          const float4 ns = __ldg(row_ptr(a.n4, a.pitch4, y) + x);
-          if (!(vs.z == 0)) { v = make_float3(vs.x, vs.y, vs.z); n = make_float3(ns.x, ns.y, ns.z); }
-          row_ptr(a.zdepth, a.pitch[0], y)[x] = (vs.z > a.zcut || vs.z <= 0) ? qnan() : vs.z;
-          store_plane3(a.vmap[0], a.pitch[0], a.rows[0], y, x, xform_v<TRANSFORM>(a, v));
-          store_plane3(a.nmap[0], a.pitch[0], a.rows[0], y, x, xform_n<TRANSFORM>(a, n));
-        }
-        v0[q] = v; n0[q] = n;
-      }
-      const int x1 = bx * 2 + sx, y1 = by * 2 + sy;
-      const float3 vv = box4(v0[0], v0[1], v0[2], v0[3], false);
-      const float3 nn = box4(n0[0], n0[1], n0[2], n0[3], true);
-      v1[sy * 2 + sx] = vv; n1[sy * 2 + sx] = nn;
-      if (x1 < a.cols[1] && y1 < a.rows[1]) {
-        store_plane3(a.vmap[1], a.pitch[1], a.rows[1], y1, x1, xform_v<TRANSFORM>(a, vv));
-        store_plane3(a.nmap[1], a.pitch[1], a.rows[1], y1, x1, xform_n<TRANSFORM>(a, nn));
-      }
+  for (int r = 0; r < 2; ++r) {
+    const int y = y0 + r;
+    if (y >= a.rows[0] || x0 >= a.cols[0]) continue;
+    const float3 va = xform_v<TRANSFORM>(a, v0[2 * r]), na = xform_n<TRANSFORM>(a, n0[2 * r]);
+    if (x0 + 1 < a.cols[0]) {
+      store_plane3_pair(a.vmap[0], a.pitch[0], a.rows[0], y, x0, va, xform_v<TRANSFORM>(a, v0[2 * r + 1]));
+      store_plane3_pair(a.nmap[0], a.pitch[0], a.rows[0], y, x0, na, xform_n<TRANSFORM>(a, n0[2 * r + 1]));
+    } else {
+      store_plane3(a.vmap[0], a.pitch[0], a.rows[0], y, x0, va);
+      store_plane3(a.nmap[0], a.pitch[0], a.rows[0], y, x0, na);
     }
   }
-  if (bx < a.cols[2] && by < a.rows[2]) {
-    const float3 vv = box4(v1[0], v1[1], v1[2], v1[3], false);
-    const float3 nn = box4(n1[0], n1[1], n1[2], n1[3], true);
-    store_plane3(a.vmap[2], a.pitch[2], a.rows[2], by, bx, xform_v<TRANSFORM>(a, vv));
-    store_plane3(a.nmap[2], a.pitch[2], a.rows[2], by, bx, xform_n<TRANSFORM>(a, nn));
+  const float3 vv = box4(v0[0], v0[1], v0[2], v0[3], false);
+  const float3 nn = box4(n0[0], n0[1], n0[2], n0[3], true);
+  if (x1 < a.cols[1] && y1 < a.rows[1]) {
+    store_plane3(a.vmap[1], a.pitch[1], a.rows[1], y1, x1, xform_v<TRANSFORM>(a, vv));
+    store_plane3(a.nmap[1], a.pitch[1], a.rows[1], y1, x1, xform_n<TRANSFORM>(a, nn));
+  }
+  // level 2: the 2x2 level-1 values sit in lanes l, l+1, l+16, l+17 (l = even lx of the upper row)
+  const float3 vb = shfl3(vv, lane + 1), vc = shfl3(vv, lane + 16), vd = shfl3(vv, lane + 17);
+  const float3 nb = shfl3(nn, lane + 1), nc = shfl3(nn, lane + 16), nd = shfl3(nn, lane + 17);
+  const int x2 = x1 >> 1, y2 = y1 >> 1;
+  if ((lane & 17) == 0 && x2 < a.cols[2] && y2 < a.rows[2]) {
+    store_plane3(a.vmap[2], a.pitch[2], a.rows[2], y2, x2, xform_v<TRANSFORM>(a, box4(vv, vb, vc, vd, false)));
+    store_plane3(a.nmap[2], a.pitch[2], a.rows[2], y2, x2, xform_n<TRANSFORM>(a, box4(nn, nb, nc, nd, true)));
   }
 }
 
@@ -100,8 +114,8 @@ cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4
     a.nmap[i] = use_prev ? lv[i].nmap_prev : lv[i].nmap_curr;
     a.pitch[i] = lv[i].pitch_f32; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols;
   }
-  const dim3 block(32, 4);
-  const dim3 grid(((lv[0].cols + 3) / 4 + 31) / 32, ((lv[0].rows + 3) / 4 + 3) / 4);
+  const dim3 block(128);
+  const dim3 grid(((lv[0].cols + 1) / 2 + 31) / 32, ((lv[0].rows + 1) / 2 + 3) / 4);
   if (pose16_or_null) {
     const float* p = pose16_or_null;
     a.R.r[0] = make_float3(p[0], p[1], p[2]); a.R.r[1] = make_float3(p[4], p[5], p[6]); a.R.r[2] = make_float3(p[8], p[9], p[10]);
