@@ -143,6 +143,43 @@ struct PopArgs {
   int pitch_f[3], pitch_i[3], rows[3], cols[3];
 };
 
+// One output of pyrDownGaussF / pyrDownUcharGauss (cf.cu:416-443, 544-573) from shared tiles.  The window is
+// [cx0, tx) x [cy0, ty) with the weight of tap (cx, cy) taken at (tx - cx - 1, ty - cy - 1).  The counts
+// are sums of the integer weights (the reference adds them in float and truncates: exact), so they are kept as ints.
+// FULL = the 5x5 window lies inside the image: fixed trip counts, weights as immediates.
+template <bool HAS_DEPTH, bool FULL, int TS_D, int TS_I>
+__device__ __forceinline__ void gauss_tap_window(const float* sd, const unsigned char* si, int lx0, int ly0, int nx, int ny, float* sumd_o, int* cntd_o,
+                                                 float* sumi_o, int* cnti_o) {
+  float sumd = 0.f, sumi = 0.f; int cntd = 0, cnti = 0;
+  if (FULL) {
+#pragma unroll
+    for (int r = 0; r < 5; ++r)
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const int gi = ((r == 0 || r == 4) ? 1 : ((r == 1 || r == 3) ? 4 : 6)) * ((c == 0 || c == 4) ? 1 : ((c == 1 || c == 3) ? 4 : 6));  // symmetric: index order irrelevant
+        const float g = (float)gi;
+        const unsigned char iv = si[(ly0 + r) * TS_I + lx0 + c];
+        if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti += gi; }
+        if (HAS_DEPTH) {
+          const float v = sd[(ly0 + r) * TS_D + lx0 + c];
+          if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd += gi; }
+        }
+      }
+  } else {
+    for (int r = 0; r < ny; ++r)
+      for (int c = 0; c < nx; ++c) {
+        const float g = c_gauss5[(ny - r - 1) * 5 + (nx - c - 1)];
+        const unsigned char iv = si[(ly0 + r) * TS_I + lx0 + c];
+        if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti = __float2int_rz(fadd((float)cnti, g)); }
+        if (HAS_DEPTH) {
+          const float v = sd[(ly0 + r) * TS_D + lx0 + c];
+          if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd = __float2int_rz(fadd((float)cntd, g)); }
+        }
+      }
+  }
+  *sumd_o = sumd; *cntd_o = cntd; *sumi_o = sumi; *cnti_o = cnti;
+}
+
 template <bool HAS_DEPTH>
 __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
   __shared__ float sd0[41][41];
@@ -172,17 +209,9 @@ __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
     if (x < 0 || y < 0 || x >= a.cols[1] || y >= a.rows[1]) continue;
     const int tx = min(2 * x - 2 + 5, a.cols[0] - 1), ty = min(2 * y - 2 + 5, a.rows[0] - 1);
     const int cx0 = max(0, 2 * x - 2), cy0 = max(0, 2 * y - 2);
-    float sumd = 0.f, sumi = 0.f; int cntd = 0, cnti = 0;
-    for (int cy = cy0; cy < ty; ++cy)
-      for (int cx = cx0; cx < tx; ++cx) {
-        const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
-        const unsigned char iv = si0[cy - oy0][cx - ox0];
-        if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti = __float2int_rz(fadd((float)cnti, g)); }
-        if (HAS_DEPTH) {
-          const float v = sd0[cy - oy0][cx - ox0];
-          if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd = __float2int_rz(fadd((float)cntd, g)); }
-        }
-      }
+    float sumd, sumi; int cntd, cnti;
+    if (tx - cx0 == 5 && ty - cy0 == 5) gauss_tap_window<HAS_DEPTH, true, 41, 44>(&sd0[0][0], &si0[0][0], cx0 - ox0, cy0 - oy0, 5, 5, &sumd, &cntd, &sumi, &cnti);
+    else gauss_tap_window<HAS_DEPTH, false, 41, 44>(&sd0[0][0], &si0[0][0], cx0 - ox0, cy0 - oy0, tx - cx0, ty - cy0, &sumd, &cntd, &sumi, &cnti);
     const unsigned char iv1 = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));  // 0/0 -> NaN -> 0
     si1[ly][lx] = iv1;
     float d1 = 0.f;
@@ -199,17 +228,9 @@ __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
     if (x < a.cols[2] && y < a.rows[2]) {
       const int tx = min(2 * x - 2 + 5, a.cols[1] - 1), ty = min(2 * y - 2 + 5, a.rows[1] - 1);
       const int cx0 = max(0, 2 * x - 2), cy0 = max(0, 2 * y - 2);
-      float sumd = 0.f, sumi = 0.f; int cntd = 0, cnti = 0;
-      for (int cy = cy0; cy < ty; ++cy)
-        for (int cx = cx0; cx < tx; ++cx) {
-          const float g = c_gauss5[(ty - cy - 1) * 5 + (tx - cx - 1)];
-          const unsigned char iv = si1[cy - oy1][cx - ox1];
-          if (iv > 0) { sumi = ffma((float)(int)iv, g, sumi); cnti = __float2int_rz(fadd((float)cnti, g)); }
-          if (HAS_DEPTH) {
-            const float v = sd1[cy - oy1][cx - ox1];
-            if (!isnan(v)) { sumd = ffma(v, g, sumd); cntd = __float2int_rz(fadd((float)cntd, g)); }
-          }
-        }
+      float sumd, sumi; int cntd, cnti;
+      if (tx - cx0 == 5 && ty - cy0 == 5) gauss_tap_window<HAS_DEPTH, true, 19, 20>(&sd1[0][0], &si1[0][0], cx0 - ox1, cy0 - oy1, 5, 5, &sumd, &cntd, &sumi, &cnti);
+      else gauss_tap_window<HAS_DEPTH, false, 19, 20>(&sd1[0][0], &si1[0][0], cx0 - ox1, cy0 - oy1, tx - cx0, ty - cy0, &sumd, &cntd, &sumi, &cnti);
       row_ptr(a.img[2], a.pitch_i[2], y)[x] = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));
       if (HAS_DEPTH) row_ptr(a.depth[2], a.pitch_f[2], y)[x] = fdiv(sumd, (float)cntd);
     }
@@ -247,6 +268,22 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
   const int x_mi = max(0, 2 * x - 2) - 2 * x, y_mi = max(0, 2 * y - 2) - 2 * y;
   const int x_ma = min(scols, 2 * x - 2 + 5) - 2 * x, y_ma = min(srows, 2 * y - 2 + 5) - 2 * y;
   float sum = 0.0f, wall = 0.0f;
+  if (x_mi == -2 && y_mi == -2 && x_ma == 3 && y_ma == 3) {  // whole 5x5 window inside the image: fixed trip counts, immediate weights
+#pragma unroll
+    for (int yi = -2; yi <= 2; ++yi) {
+      const float wy = (yi == 0) ? 0.375f : ((yi == 1 || yi == -1) ? 0.25f : 0.0625f);
+#pragma unroll
+      for (int xi = -2; xi <= 2; ++xi) {
+        const int val = tile[(2 * y + yi - oy) * tstride + (2 * x + xi - ox)];
+        if ((float)abs(val - center) < 90.0f) {
+          const float wx = (xi == 0) ? 0.375f : ((xi == 1 || xi == -1) ? 0.25f : 0.0625f);
+          sum = ffma(fmul((float)val, wx), wy, sum);
+          wall = ffma(wx, wy, wall);
+        }
+      }
+    }
+    return (unsigned short)__float2int_rz(fdiv(sum, wall));
+  }
   for (int yi = y_mi; yi < y_ma; ++yi) {
     const float wy = (yi == 0) ? 0.375f : (abs(yi) == 1 ? 0.25f : 0.0625f);
     for (int xi = x_mi; xi < x_ma; ++xi) {
