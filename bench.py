@@ -177,7 +177,26 @@ def run_legacy_frames(cam, frames, n_frames, budget_s):
         return {"unavailable": repr(e)}
 
 
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """Libraries (NCCL's version banner, OpenMP) may write to fd 1; the contract is ONE JSON line on stdout.  Everything
+    else goes to stderr, the JSON line to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=1000)
@@ -211,13 +230,13 @@ def main():
         done, secs, threads = run_oracle_frames(cam, frames, args.steps, 150.0)
         fps = done / secs
         sample = f"{done} of {args.steps} frames (time-bounded), same per-frame call sequence"
-        print(json.dumps({
+        emit({
             "impl": "reference", "metric": "odometry_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 / fps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": config,
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "note": "the reference has no CPU implementation of this path; this is the OpenMP transcription of its equations (oracle/cpu_odom.cpp)"}))
+            "note": "the reference has no CPU implementation of this path; this is the OpenMP transcription of its equations (oracle/cpu_odom.cpp)"})
         return
 
     # ------------------------------------------------------------------ our arm (GPU)
@@ -359,7 +378,7 @@ def main():
     roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, depth)
 
     if args.quick:
-        print(json.dumps({"value": value, "roofline": roofline, "config": config, "clocks": clocks}))
+        emit({"value": value, "roofline": roofline, "config": config, "clocks": clocks})
         return
     e2e_steps = min(args.steps, 300)
     ms_e2e, _, _, _, _, _ = timed(pipe, e2e_steps, min(args.warmup, 5), True)
@@ -410,7 +429,7 @@ def main():
         if legacy:
             out["legacy_cuda"] = legacy
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
