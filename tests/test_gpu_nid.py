@@ -47,3 +47,37 @@ def test_nid_score_matches_restatement(level, nb_img, nb_depth):
     mi.setKeyFrame(dev(torch, live["vmap4"]), dev(torch, live["rgba"]), dev(torch, live["vmap4"]), dev(torch, live["rgba"]), cutoff)
     ni_self, _, _ = mi.score(g, cutoff, lam)
     assert ni_self < ni
+
+
+def test_nid_ragged_size_and_stateless_entry_points():
+    """Odd image size at pyramid level 2; dms_nid_image / dms_nid_depth on caller-owned buffers."""
+    import ctypes as C
+    import torch
+    from densemonoslam_b200 import _lib
+    from oracle import nid_ref
+    rng = np.random.RandomState(5)
+    H, W = 61, 83
+    ik = rng.randint(0, 256, (H, W)).astype(np.uint8); iko = rng.randint(0, 256, (H, W)).astype(np.uint8); ic = rng.randint(0, 256, (H, W)).astype(np.uint8)
+    dk = rng.uniform(0.4, 3.4, (H, W)).astype(np.float32); dko = rng.uniform(0.4, 3.4, (H, W)).astype(np.float32); dc = rng.uniform(0.4, 3.4, (H, W)).astype(np.float32)
+    for a in (dk, dko, dc):
+        a[rng.rand(H, W) < 0.1] = np.nan
+    L = _lib.load()
+    t = lambda a: torch.from_numpy(a).cuda()
+    tik, tiko, tic, tdk, tdko, tdc = t(ik), t(iko), t(ic), t(dk), t(dko), t(dc)
+    for nb_i, nb_d in ((64, 500), (16, 50), (128, 1000)):
+        hist = torch.zeros(max(nb_i, nb_d) * (max(nb_i, nb_d) + 2), dtype=torch.int32, device="cuda"); out = torch.zeros(4, device="cuda")
+        v = C.c_float()
+        rc = L.dms_nid_image(C.c_void_p(tik.data_ptr()), C.c_void_p(tiko.data_ptr()), C.c_void_p(tdk.data_ptr()), C.c_void_p(tdko.data_ptr()),
+                             C.c_void_p(tic.data_ptr()), W, W * 4, W, H, W, nb_i, C.c_void_p(hist.data_ptr()), C.c_void_p(out.data_ptr()), C.byref(v), None)
+        assert rc == 0
+        hi = nid_ref.hist_img(ik, iko, dk, dko, ic, nb_i)
+        assert np.array_equal(hist[: nb_i * nb_i].cpu().numpy().reshape(nb_i, nb_i).astype(np.int64), hi)
+        ref = float(nid_ref.nid_from_hist(hi, H * W))
+        assert abs(v.value - ref) <= 1e-4 * abs(ref) + 1e-6
+        rc = L.dms_nid_depth(C.c_void_p(tdk.data_ptr()), C.c_void_p(tdko.data_ptr()), C.c_void_p(tdc.data_ptr()), W * 4, W * 4, H, W, nb_d, 3500.0,
+                             C.c_void_p(hist.data_ptr()), C.c_void_p(out.data_ptr()), C.byref(v), None)
+        assert rc == 0
+        hd = nid_ref.hist_depth(dk, dko, dc, nb_d, 3500.0)
+        assert np.array_equal(hist[: nb_d * nb_d].cpu().numpy().reshape(nb_d, nb_d).astype(np.int64), hd)
+        ref = float(nid_ref.nid_from_hist(hd, H * W))
+        assert abs(v.value - ref) <= 1e-4 * abs(ref) + 1e-6

@@ -92,3 +92,33 @@ def test_front_end_tracks_against_splatted_map():
     e_est = [np.linalg.norm(rel(est[i], est[i + 1])[:3, 3] - rel(gt[i], gt[i + 1])[:3, 3]) for i in range(len(gt) - 1)]
     e_pri = [np.linalg.norm(rel(pri[i], pri[i + 1])[:3, 3] - rel(gt[i], gt[i + 1])[:3, 3]) for i in range(len(gt) - 1)]
     assert np.mean(e_est) < 0.3 * np.mean(e_pri), (e_est, e_pri)
+
+
+def test_splat_edge_cases():
+    """Empty map, a surfel right in front of the camera (sprite larger than the image), surfels on the image border,
+    behind the camera and edge-on; ragged image size."""
+    import torch
+    from densemonoslam_b200 import splat
+    from oracle import splat_ref as sr
+    rows, cols = 37, 53
+    c = (25.7, 18.2, 40.0, 41.0)
+    I = np.eye(4, dtype=np.float32)
+    kw = dict(depthCutoff=5.0, confThreshold=1.0, time=3, timeIdx=1, maxTime=3, timeDelta=10)
+    empty = torch.zeros((0, 15), dtype=torch.float32, device="cuda")
+    gi, gv, gn, gt = splat.combinedPredict(empty, I, c, rows, cols, predictionType=1, t_inv=I, **kw)
+    assert not gi.any() and not gv.any() and not gn.any() and not gt.any()
+
+    def surfel(x, y, z, rad, n, col=0x102030):
+        s = np.zeros(15, np.float32); s[0:4] = (x, y, z, 9.0); s[4] = col; s[6] = 2; s[8:11] = (-3, 2, -3); s[11:14] = n; s[14] = rad
+        return s
+    S = np.stack([surfel(0.0, 0.0, 0.05, 0.5, (0, 0, -1), 0x0000ff),            # fills the whole view
+                  surfel(-1.2, 0.3, 2.0, 0.2, (0.3, 0, -0.95)),                  # centre just outside the left border: clipped
+                  surfel(1.25, -0.8, 2.0, 0.15, (0, 0.2, -0.98), 0x00ff00),      # near the top-right corner
+                  surfel(0.1, 0.1, -1.0, 0.1, (0, 0, -1)),                       # behind the camera
+                  surfel(0.3, 0.2, 0.04, 0.05, (1, 0, 0), 0xff0000),             # edge-on, nearer than the big one
+                  surfel(-0.2, 0.1, 0.03, 0.004, (0.1, -0.2, -0.97), 0xffff00)])  # small, nearest
+    gi, gv, gn, gt = splat.combinedPredict(torch.from_numpy(S).cuda(), I, c, rows, cols, predictionType=1, t_inv=I, **kw)
+    oi, ov, on, ot = sr.predict(S, I, c, rows, cols, 5.0, 1.0, 3, 1, 3, 10, 1)
+    assert np.array_equal(gi.cpu().numpy(), oi) and np.array_equal(gt.cpu().numpy().astype(np.uint32), ot)
+    assert np.array_equal(bits(gv.cpu().numpy()), bits(ov)) and np.array_equal(bits(gn.cpu().numpy()), bits(on))
+    assert (ov[..., 2] > 0).mean() > 0.9   # the big surfel covers the image
