@@ -64,56 +64,88 @@ __global__ void __launch_bounds__(256) k_nid_hist_depth(const float* dk, const f
     const float b = fmul(__ldg(row_ptr(dc, pc, y) + x), 1000.0f);
     const int ba = nid_depth_bin(a, bw), bb = nid_depth_bin(b, bw);
     if (ba < 0 || bb < 0 || ba >= nb || bb >= nb) continue;  // out of bounds in the reference
-    atomicAdd(&hist[bb * nb + ba], 1u);
+    // neighbouring pixels mostly fall into the same bin pair: one atomic per distinct pair of the warp
+    const int key = bb * nb + ba;
+    const unsigned int peers = __match_any_sync(__activemask(), key);
+    if ((int)(__ffs((int)peers) - 1) == lane) atomicAdd(&hist[key], (unsigned int)__popc(peers));
   }
 }
 
-// Entropies and the score (cf.cu:1556-1615), one CTA.  p = count / num_points in fp32, p * log2f(p) in fp32, the
-// three sums in fp64.  out[0] = nid, out[1] = joint entropy, out[2] = key-frame marginal, out[3] = live marginal.
-__global__ void __launch_bounds__(1024) k_nid_entropy(const unsigned int* hist, int nb, int num_points, unsigned int* marg, float* out) {
-  __shared__ double red[32];
-  const int t = threadIdx.x, n2 = nb * nb;
-  const float np = (float)num_points;
-  // marginal counts (integers): marg[0..nb) = columns (key frame, P_B), marg[nb..2nb) = rows (live frame, P_A)
-  for (int i = t; i < 2 * nb; i += blockDim.x) marg[i] = 0u;
+// Entropies and the score (cf.cu:1556-1615).  p = count / num_points in fp32, p * log2f(p) in fp32, sums in fp64.
+// Pass 1 (one CTA per group of histogram rows): joint-entropy and live-marginal partial sums per CTA, key-frame
+// marginal counts (columns) by integer atomics.  Pass 2 (one CTA): key-frame marginal entropy, the partial sums in
+// CTA order (deterministic), the score.  out[0] = nid, out[1] = joint entropy, out[2] = key-frame, out[3] = live.
+static const int NID_ENT_CTAS = 128;
+__device__ __forceinline__ double block_sum(double s, double* red) {
+  const int t = threadIdx.x;
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
   __syncthreads();
-  double joint = 0.0;
-  for (int i = t; i < n2; i += blockDim.x) {
-    const unsigned int c = hist[i];
-    if (c) {
-      const int r = i / nb, col = i - r * nb;
-      atomicAdd(&marg[col], c); atomicAdd(&marg[nb + r], c);
-      const float p = fdiv((float)c, np);
-      joint += (double)fmul(p, log2f(p));
-    }
-  }
+  if ((t & 31) == 0) red[t >> 5] = s;
   __syncthreads();
-  double kf = 0.0, cf = 0.0;
-  for (int i = t; i < nb; i += blockDim.x) {
-    const unsigned int a = marg[i], b = marg[nb + i];
-    if (a) { const float p = fdiv((float)a, np); kf += (double)fmul(p, log2f(p)); }
-    if (b) { const float p = fdiv((float)b, np); cf += (double)fmul(p, log2f(p)); }
-  }
-  double v[3] = {joint, kf, cf};
-  float res[3];
-  for (int k = 0; k < 3; ++k) {
-    double s = v[k];
+  if (t < 32) {
+    s = t < (int)(blockDim.x >> 5) ? red[t] : 0.0;
     for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-    __syncthreads();
-    if ((t & 31) == 0) red[t >> 5] = s;
-    __syncthreads();
-    if (t < 32) {
-      s = t < (int)(blockDim.x >> 5) ? red[t] : 0.0;
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-    }
-    res[k] = (float)(-s);
   }
+  return s;  // valid in thread 0
+}
+__global__ void __launch_bounds__(256) k_nid_entropy_rows(const unsigned int* hist, int nb, int num_points, unsigned int* colsum, double* partial) {
+  __shared__ double red[32];
+  __shared__ unsigned int rowsum;
+  const int t = threadIdx.x;
+  const float np = (float)num_points;
+  double joint = 0.0, cf = 0.0;
+  for (int r = blockIdx.x; r < nb; r += gridDim.x) {
+    if (t == 0) rowsum = 0u;
+    __syncthreads();
+    unsigned int mine = 0u;
+    for (int col = t; col < nb; col += blockDim.x) {
+      const unsigned int c = hist[(size_t)r * nb + col];
+      if (c) {
+        mine += c;
+        atomicAdd(&colsum[col], c);
+        const float p = fdiv((float)c, np);
+        joint += (double)fmul(p, log2f(p));
+      }
+    }
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((t & 31) == 0 && mine) atomicAdd(&rowsum, mine);
+    __syncthreads();
+    if (t == 0 && rowsum) { const float p = fdiv((float)rowsum, np); cf += (double)fmul(p, log2f(p)); }
+    __syncthreads();
+  }
+  const double js = block_sum(joint, red);
+  if (t == 0) { partial[2 * blockIdx.x] = js; partial[2 * blockIdx.x + 1] = cf; }
+}
+__global__ void __launch_bounds__(256) k_nid_entropy_final(const unsigned int* colsum, int nb, int num_points, const double* partial, int nparts, float* out) {
+  __shared__ double red[32];
+  const int t = threadIdx.x;
+  const float np = (float)num_points;
+  double kf = 0.0;
+  for (int i = t; i < nb; i += blockDim.x) {
+    const unsigned int a = colsum[i];
+    if (a) { const float p = fdiv((float)a, np); kf += (double)fmul(p, log2f(p)); }
+  }
+  const double kfs = block_sum(kf, red);
+  // the per-CTA partial sums: fixed tree (thread i takes partial i), hence deterministic
+  const double joint = block_sum(t < nparts ? partial[2 * t] : 0.0, red);
+  const double cf = block_sum(t < nparts ? partial[2 * t + 1] : 0.0, red);
   if (t == 0) {
-    const float joint_entropy = res[0], kf_e = res[1], cf_e = res[2];
+    const float joint_entropy = (float)(-joint), kf_e = (float)(-kfs), cf_e = (float)(-cf);
     const float mutual = fsub(fadd(kf_e, cf_e), joint_entropy);
     out[0] = num_points == 0 ? 1.0f : fdiv(fsub(joint_entropy, mutual), joint_entropy);
     out[1] = joint_entropy; out[2] = kf_e; out[3] = cf_e;
   }
+}
+// marg: nb u32 column sums followed (8-byte aligned) by 2 * NID_ENT_CTAS doubles
+static size_t nid_marg_bytes(int nb) { return ((size_t)nb * 4 + 7) / 8 * 8 + 2 * NID_ENT_CTAS * sizeof(double); }
+static cudaError_t launch_nid_entropy(const unsigned int* hist, int nb, int num_points, unsigned int* marg, float* out, cudaStream_t s) {
+  double* partial = reinterpret_cast<double*>(reinterpret_cast<char*>(marg) + ((size_t)nb * 4 + 7) / 8 * 8);
+  cudaError_t e = cudaMemsetAsync(marg, 0, (size_t)nb * 4, s);
+  if (e != cudaSuccess) return e;
+  const int ctas = nb < NID_ENT_CTAS ? nb : NID_ENT_CTAS;
+  k_nid_entropy_rows<<<ctas, 256, 0, s>>>(hist, nb, num_points, marg, partial);
+  k_nid_entropy_final<<<1, 256, 0, s>>>(marg, nb, num_points, partial, ctas, out);
+  return cudaGetLastError();
 }
 
 static int nid_grid() {
@@ -168,8 +200,8 @@ int dms_nid_create(dms_nid** out, int device, int width, int height, int pyr_lev
   }
   const size_t zbytes = al((size_t)height * h->lv[0].pitch_f32);
   const size_t hi = al((size_t)nb_img * nb_img * 4), hd = al((size_t)nb_depth * nb_depth * 4);
-  const size_t mg = al((size_t)2 * (nb_img > nb_depth ? nb_img : nb_depth) * 4);
-  total += zbytes + hi + hd + mg + 256;
+  const size_t mg = al(nid_marg_bytes(nb_img > nb_depth ? nb_img : nb_depth));
+  total += zbytes + hi + hd + 2 * mg + 256;
   cudaError_t e = cudaMalloc(&h->slab, total);
   if (e == cudaSuccess) e = cudaMemset(h->slab, 0, total);
   if (e == cudaSuccess) e = cudaMallocHost(&h->h_out, 64);
@@ -185,7 +217,7 @@ int dms_nid_create(dms_nid** out, int device, int width, int height, int pyr_lev
   h->zsrc = (float*)p; p += zbytes;
   h->hist_img = (unsigned int*)p; p += hi;
   h->hist_depth = (unsigned int*)p; p += hd;
-  h->marg = (unsigned int*)p; p += mg;
+  h->marg = (unsigned int*)p; p += 2 * mg;  // one block per histogram
   h->d_out = (float*)p;
   *out = h;
   return DMS_OK;
@@ -208,8 +240,7 @@ int dms_nid_set_keyframe(dms_nid* h, const float* v4, const uint8_t* rgba, const
 }
 
 static int nid_finish(const unsigned int* hist, int nb, int num_points, unsigned int* marg, float* d_out, float* nid, cudaStream_t s) {
-  k_nid_entropy<<<1, 1024, 0, s>>>(hist, nb, num_points, marg, d_out);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_nid_entropy(hist, nb, num_points, marg, d_out, s);
   float r[4];
   if (e == cudaSuccess) e = cudaMemcpyAsync(r, d_out, sizeof(r), cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
@@ -224,7 +255,7 @@ int dms_nid_image(const uint8_t* ik, const uint8_t* iko, const float* dk, const 
   if (!ik || !iko || !dk || !dko || !ic || !d_hist || !d_out || !nid || rows <= 0 || cols <= 0 || nb <= 0 || nb > 256) return DMS_ERR_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   // histogram + 2*nb marginal words (the caller's scratch holds nb*nb + 2*nb words)
-  cudaError_t e = cudaMemsetAsync(d_hist, 0, ((size_t)nb * nb + 2 * (size_t)nb) * 4, s);
+  cudaError_t e = cudaMemsetAsync(d_hist, 0, (size_t)nb * nb * 4, s);
   if (e != cudaSuccess) return (int)e;
   if (nb <= NID_SMEM_BINS)
     k_nid_hist_img<true><<<nid_grid(), 256, 0, s>>>(ik, iko, dk, dko, ic, (int)p8, (int)pf, (int)pc, rows, cols, nb, d_hist);
@@ -232,7 +263,7 @@ int dms_nid_image(const uint8_t* ik, const uint8_t* iko, const float* dk, const 
     k_nid_hist_img<false><<<nid_grid(), 256, 0, s>>>(ik, iko, dk, dko, ic, (int)p8, (int)pf, (int)pc, rows, cols, nb, d_hist);
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
-  return nid_finish(d_hist, nb, rows * cols, d_hist + (size_t)nb * nb, d_out, nid, s);
+  return nid_finish(d_hist, nb, rows * cols, d_hist + ((size_t)nb * nb + 1) / 2 * 2, d_out, nid, s);
 }
 
 int dms_nid_depth(const float* dk, const float* dko, const float* dc, size_t pf, size_t pc, int rows, int cols, int nb, float max_depth_mm, uint32_t* d_hist,
@@ -240,12 +271,12 @@ int dms_nid_depth(const float* dk, const float* dko, const float* dc, size_t pf,
   if (!dk || !dko || !dc || !d_hist || !d_out || !nid || rows <= 0 || cols <= 0 || nb <= 0 || nb > 4096) return DMS_ERR_INVALID;
   if ((int)(max_depth_mm / (float)nb) <= 0) return DMS_ERR_INVALID;  // bin width 0: the reference divides by zero
   cudaStream_t s = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(d_hist, 0, ((size_t)nb * nb + 2 * (size_t)nb) * 4, s);
+  cudaError_t e = cudaMemsetAsync(d_hist, 0, (size_t)nb * nb * 4, s);
   if (e != cudaSuccess) return (int)e;
   k_nid_hist_depth<<<nid_grid(), 256, 0, s>>>(dk, dko, dc, (int)pf, (int)pc, rows, cols, nb, max_depth_mm, d_hist);
   e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
-  return nid_finish(d_hist, nb, rows * cols, d_hist + (size_t)nb * nb, d_out, nid, s);
+  return nid_finish(d_hist, nb, rows * cols, d_hist + ((size_t)nb * nb + 1) / 2 * 2, d_out, nid, s);
 }
 
 int dms_nid_score(dms_nid* h, dms_odom* tracker, float max_depth_m, float lambda, float* nid_img, float* nid_depth, float* score, void* stream) {
@@ -275,9 +306,9 @@ int dms_nid_score(dms_nid* h, dms_odom* tracker, float max_depth_m, float lambda
   if ((int)(max_mm / (float)h->nb_depth) <= 0) return DMS_ERR_INVALID;
   k_nid_hist_depth<<<nid_grid(), 256, 0, s>>>(L.lastDepth, L.nextDepth, (const float*)pd, L.pitch_f32, (int)pitch_d, L.rows, L.cols, h->nb_depth, max_mm,
                                               h->hist_depth);
-  k_nid_entropy<<<1, 1024, 0, s>>>(h->hist_img, h->nb_img, L.rows * L.cols, h->marg, h->d_out);
-  k_nid_entropy<<<1, 1024, 0, s>>>(h->hist_depth, h->nb_depth, L.rows * L.cols, h->marg, h->d_out + 4);
-  e = cudaGetLastError();
+  const size_t mgw = (nid_marg_bytes(h->nb_img > h->nb_depth ? h->nb_img : h->nb_depth) + 255) / 256 * 256 / 4;
+  e = launch_nid_entropy(h->hist_img, h->nb_img, L.rows * L.cols, h->marg, h->d_out, s);
+  if (e == cudaSuccess) e = launch_nid_entropy(h->hist_depth, h->nb_depth, L.rows * L.cols, h->marg + mgw, h->d_out + 4, s);
   if (e == cudaSuccess) e = cudaMemcpyAsync(h->h_out, h->d_out, 32, cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) return (int)e;

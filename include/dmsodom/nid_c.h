@@ -36,7 +36,9 @@ int dms_nid_score(dms_nid* h, dms_odom* tracker, float max_depth_m, float depth_
 int dms_nid_get_histogram(dms_nid* h, int which, uint32_t* h_dst, size_t n_words, void* stream);
 
 /* Stateless forms of computeNIDImg (cf.cu:1513-1650) / computeNIDDepth (cf.cu:1794-1915) on pitched device images.
- * d_hist: num_bins * (num_bins + 2) u32 of device scratch (histogram + marginals, cleared by the call), d_out: 4 floats. */
+ * d_hist: DMS_NID_SCRATCH_WORDS(num_bins) u32 of 8-byte aligned device scratch (histogram, marginals, partial sums;
+ * cleared by the call), d_out: 4 floats. */
+#define DMS_NID_SCRATCH_WORDS(nb) ((size_t)(nb) * (nb) + (nb) + 520)
 int dms_nid_image(const uint8_t* d_img_kf, const uint8_t* d_img_kf_old, const float* d_dmap_kf, const float* d_dmap_kf_old,
                   const uint8_t* d_img_curr, size_t pitch_u8, size_t pitch_f32, size_t pitch_curr, int rows, int cols,
                   int num_bins, uint32_t* d_hist, float* d_out, float* nid, void* stream);

@@ -65,7 +65,9 @@ def test_nid_ragged_size_and_stateless_entry_points():
     t = lambda a: torch.from_numpy(a).cuda()
     tik, tiko, tic, tdk, tdko, tdc = t(ik), t(iko), t(ic), t(dk), t(dko), t(dc)
     for nb_i, nb_d in ((64, 500), (16, 50), (128, 1000)):
-        hist = torch.zeros(max(nb_i, nb_d) * (max(nb_i, nb_d) + 2), dtype=torch.int32, device="cuda"); out = torch.zeros(4, device="cuda")
+        nbm = max(nb_i, nb_d)
+        hist = torch.zeros(nbm * nbm + nbm + 520, dtype=torch.int32, device="cuda")   # DMS_NID_SCRATCH_WORDS
+        out = torch.zeros(4, device="cuda")
         v = C.c_float()
         rc = L.dms_nid_image(C.c_void_p(tik.data_ptr()), C.c_void_p(tiko.data_ptr()), C.c_void_p(tdk.data_ptr()), C.c_void_p(tdko.data_ptr()),
                              C.c_void_p(tic.data_ptr()), W, W * 4, W, H, W, nb_i, C.c_void_p(hist.data_ptr()), C.c_void_p(out.data_ptr()), C.byref(v), None)
