@@ -64,9 +64,11 @@ __device__ __forceinline__ SplatVert splat_vertex(const float* s, const SplatK& 
 }
 
 // combo_splat.frag:36-66 at pixel (i, j); returns false when the fragment is discarded / clipped
-__device__ __forceinline__ bool splat_fragment(const SplatVert& v, const SplatK& k, int i, int j, float* z_out, unsigned int* d24) {
-  const float fxc = fadd((float)i, 0.5f), fyc = fadd((float)j, 0.5f);
-  const float3 l = normalize3u(make_float3(fdiv(fsub(fxc, k.cx), k.fx), fdiv(fsub(fyc, k.cy), k.fy), 1.0f));
+// un-normalised ray components of a pixel column / row: (gl_FragCoord - cam.xy) / cam.zw
+__device__ __forceinline__ float splat_ray_x(const SplatK& k, int i) { return fdiv(fsub(fadd((float)i, 0.5f), k.cx), k.fx); }
+__device__ __forceinline__ float splat_ray_y(const SplatK& k, int j) { return fdiv(fsub(fadd((float)j, 0.5f), k.cy), k.fy); }
+__device__ __forceinline__ bool splat_fragment(const SplatVert& v, const SplatK& k, float rx, float ry, float* z_out, unsigned int* d24) {
+  const float3 l = normalize3u(make_float3(rx, ry, 1.0f));
   const float sc = fdiv(dot3u(v.pos.x, v.pos.y, v.pos.z, v.n.x, v.n.y, v.n.z), dot3u(l.x, l.y, l.z, v.n.x, v.n.y, v.n.z));
   const float3 cp = make_float3(fmul(sc, l.x), fmul(sc, l.y), fmul(sc, l.z));
   const float dx = fsub(cp.x, v.pos.x), dy = fsub(cp.y, v.pos.y), dz = fsub(cp.z, v.pos.z);
@@ -87,16 +89,39 @@ __device__ __forceinline__ void splat_box(const SplatVert& v, const SplatK& k, i
 static const unsigned long long ZBUF_EMPTY = ~0ull;
 
 __global__ void __launch_bounds__(256) k_splat_raster(const float* surfels, int count, SplatK k, unsigned long long* zbuf) {
+  extern __shared__ float s_ray[];  // cols x-components, then rows y-components: the two divisions of a fragment's ray, once per CTA
+  for (int i = threadIdx.x; i < k.cols; i += blockDim.x) s_ray[i] = splat_ray_x(k, i);
+  for (int j = threadIdx.x; j < k.rows; j += blockDim.x) s_ray[k.cols + j] = splat_ray_y(k, j);
+  __syncthreads();
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < count; idx += gridDim.x * blockDim.x) {
     const SplatVert v = splat_vertex(surfels + (size_t)idx * DMS_SURFEL_FLOATS, k);
     if (!v.visible) continue;
     int x0, x1, y0, y1;
     splat_box(v, k, &x0, &x1, &y0, &y1);
-    for (int j = y0; j <= y1; ++j)
-      for (int i = x0; i <= x1; ++i) {
-        float z; unsigned int d;
-        if (splat_fragment(v, k, i, j, &z, &d)) atomicMin(&zbuf[(size_t)j * k.cols + i], ((unsigned long long)d << 32) | (unsigned int)idx);
+    // Conservative pre-cull (never rejects a fragment the shader test accepts): a point of the disk is within rad of its
+    // centre in 3-D, so with z > rad its projection stays within f * rad * (1 + max(|x|, |y|) / z) / (z - rad) pixels of
+    // the centre's projection; 2 % + half a pixel cover the rounding of the exact test.  Rows are clipped to that circle.
+    float R2 = 3.0e38f, Rr = 3.0e38f;
+    if (v.pos.z > v.rad * 1.001f) {
+      const float f = fmaxf(k.fx, k.fy);
+      Rr = f * v.rad * (1.0f + fmaxf(fabsf(v.pos.x), fabsf(v.pos.y)) / v.pos.z) / (v.pos.z - v.rad) * 1.02f + 0.5f;
+      R2 = Rr * Rr;
+    }
+    for (int j = y0; j <= y1; ++j) {
+      const float dyp = (float)j + 0.5f - v.yw;
+      const float rem = R2 - dyp * dyp;
+      if (!(rem >= 0.0f)) continue;
+      int xa = x0, xb = x1;
+      if (Rr < 1.0e30f) {
+        const float hw = sqrtf(rem) + 0.01f;
+        xa = max(x0, (int)floorf(v.xw - hw - 0.5f)); xb = min(x1, (int)ceilf(v.xw + hw - 0.5f));
       }
+      const float ry = s_ray[k.cols + j];
+      for (int i = xa; i <= xb; ++i) {
+        float z; unsigned int d;
+        if (splat_fragment(v, k, s_ray[i], ry, &z, &d)) atomicMin(&zbuf[(size_t)j * k.cols + i], ((unsigned long long)d << 32) | (unsigned int)idx);
+      }
+    }
   }
 }
 
@@ -110,7 +135,7 @@ __global__ void __launch_bounds__(256) k_splat_resolve(const float* surfels, Spl
   if (key != ZBUF_EMPTY) {
     const SplatVert v = splat_vertex(surfels + (size_t)(unsigned int)key * DMS_SURFEL_FLOATS, k);
     float z = 0.f; unsigned int d;
-    splat_fragment(v, k, i, j, &z, &d);
+    splat_fragment(v, k, splat_ray_x(k, i), splat_ray_y(k, j), &z, &d);
     const int c = (int)v.colour;  // color.glsl:27-34; the RGBA8 attachment stores round(c / 255 * 255) = c
     im = make_uchar4((unsigned char)((c >> 16) & 0xFF), (unsigned char)((c >> 8) & 0xFF), (unsigned char)(c & 0xFF), 255);
     const float fxc = fadd((float)i, 0.5f), fyc = fadd((float)j, 0.5f);
@@ -164,7 +189,9 @@ int dms_splat_predict(const float* d_surfels, int count, const dms_splat_params*
     cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int grid = (count + 255) / 256;
     if (grid > sms * 8) grid = sms * 8;
-    k_splat_raster<<<grid, 256, 0, s>>>(d_surfels, count, k, d_zbuf);
+    const size_t ray_bytes = (size_t)(p->rows + p->cols) * sizeof(float);
+    if (ray_bytes > 48 * 1024) return DMS_ERR_TOO_LARGE;  // rows + cols <= 12288
+    k_splat_raster<<<grid, 256, ray_bytes, s>>>(d_surfels, count, k, d_zbuf);
     e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
   }
