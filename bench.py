@@ -36,7 +36,7 @@ sys.path.insert(0, ROOT)
 FLAGS = dict(rgbOnly=False, icpWeight=10.0, pyramid=True, fastOdom=False, so3=True)
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch at 1241x376 (ncu --set full, profiles/): the working
 # set is L2-resident, so DRAM traffic is far BELOW the algorithmic bytes
-TRAFFIC_NCU = 35.7e6
+TRAFFIC_NCU = 32.8e6  # dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch of this command (profiles/r01_ncu_k_track_kitti.json)
 
 
 def workload_def(name):
@@ -390,7 +390,8 @@ def main():
            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + frames[0]["live"]["rgba"].nbytes,
                    "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
-           "gpu_launches": 14 * args.steps, "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
+           "gpu_launches": 6 * args.steps,  # per frame: k_populate x3, k_maps_pyramid, k_icp_depth, k_track (profiles/r01_launches_kitti_final.csv)
+           "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
            "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
     if world > 1:
         # the only exchange of the multi-sensor mode: per-frame result records, gathered on rank 0 outside the timed region
