@@ -256,12 +256,13 @@ class OracleOdometry:
 
     def __init__(self, width, height, cx, cy, fx, fy, distThresh=0.10, angleThresh=float(np.sin(np.float32(20.0) * np.float32(3.14159254) / np.float32(180.0)))):
         self._h = lib().orc_odom_create(width, height, cx, cy, fx, fy, distThresh, angleThresh)
+        self._destroy = lib().orc_odom_destroy   # bound now: module globals may be gone at interpreter shutdown
         self.width, self.height = width, height
         self.last = None
 
     def __del__(self):
         if getattr(self, "_h", None):
-            lib().orc_odom_destroy(self._h)
+            self._destroy(self._h)
             self._h = None
 
     def initICP(self, depth_u16, depthCutoff=25.0):

@@ -73,4 +73,27 @@ o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy); o
 out["N4 nid 1241x376 level 1"] = {"set_keyframe_gpu_us": us_kf, "score_host_us (2 histograms + entropies + sync)": host_us,
                                   "cpu_oracle_ms": cpu_ms(lambda: nid_ref.nid_score(model["vmap4"], model["rgba"], model["vmap4"], model["rgba"], 25.0,
                                                                                     o.buffer("nextImage", 1), o.buffer("nextDepth", 1), 1, 64, 500, 25.0, 0.5), reps=1)}
+# whole front-end frame without GL: depth filter -> splat prediction -> FillIn / denseEnough -> frame-to-model track
+# -> second prediction + inactive prediction -> model-to-model registration and its gates
+from densemonoslam_b200.frontend import TrackingFrontEnd
+S2 = dev(S)
+
+
+def predictor(p, kind, tick):
+    img, ver, nor, _ = splat.combinedPredict(S2, p, c, cam.height, cam.width, 25.0, 5.0, 6, 0, 6, 200, splat.ACTIVE if kind != 2 else splat.ACTIVE)
+    return {"vertex": ver, "normal": nor, "image": img}
+
+
+for loops in (0, 1):
+    fe = TrackingFrontEnd(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, predictor, depthCutoff=25.0, closeLoops=loops)
+    seq = synth.kitti_sequence(cam, 6, seed=2021)
+    frames_dev = [(dev(f["live"]["rgba"]), dev(f["live"]["depth"]), f["prior"]) for f in seq]
+    fe.process(*frames_dev[0])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); n = 0
+    for rep in range(8):
+        for rgba, depth, prior in frames_dev[1:]:
+            fe.process(rgba, depth, prior); n += 1
+    ms = (time.perf_counter() - t0) * 1e3 / n
+    out[f"front end frame 1241x376, 1.3 M surfels, closeLoops={loops}"] = {"host_ms_per_frame": ms, "frames_per_s": 1000.0 / ms}
 print(json.dumps(out, indent=1))
