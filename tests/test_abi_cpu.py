@@ -63,3 +63,14 @@ def test_create_fails_loudly_without_gpu():
     from densemonoslam_b200.odometry import RGBDOdometry, DmsError
     with pytest.raises(DmsError):
         RGBDOdometry(640, 480, 320, 240, 528, 528)
+
+
+def test_headers_compile_as_c_and_cpp(tmp_path):
+    """The four C-ABI headers are plain C (and valid C++): no torch / CUDA types in the signatures."""
+    inc = os.path.join(ROOT, "include")
+    src = '#include "dmsodom/odom_c.h"\n#include "dmsodom/frontend_c.h"\n#include "dmsodom/splat_c.h"\n#include "dmsodom/nid_c.h"\nint main(void) { return 0; }\n'
+    for comp, name, std in (("gcc", "t.c", "-std=c99"), ("g++", "t.cpp", "-std=c++11")):
+        f = tmp_path / name
+        f.write_text(src)
+        r = subprocess.run([comp, std, "-Wall", "-Werror", "-fsyntax-only", "-I", inc, str(f)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr

@@ -1,0 +1,43 @@
+"""bench.py prints exactly one JSON line with the contract's keys (reference arm here on CPU, our arm on the GPU)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import ROOT
+
+BASE_KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data",
+             "config", "e2e"}
+
+
+def run(args, timeout):
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py")] + args, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, f"stdout must hold one JSON line, got {len(lines)}"
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line():
+    j = run(["--impl", "reference", "--steps", "2", "--warmup", "1"], 600)
+    assert BASE_KEYS <= set(j) and j["impl"] == "reference"
+    assert j["metric"] == "odometry_frames_per_s" and j["unit"] == "frames/s" and j["higher_is_better"] is True
+    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["value"] == j["value"] > 0
+    assert j["e2e"] == {"value": j["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in j["config"]
+
+
+@pytest.mark.gpu
+def test_our_arm_line():
+    j = run(["--steps", "16", "--warmup", "3", "--no-cpu-baseline"], 900)
+    assert BASE_KEYS | {"roofline", "gpu_launches", "clocks"} <= set(j)
+    assert j["n_gpus"] == 1 and j["steps"] == 16 and j["warmup"] == 3 and j["vs_baseline"] is None and j["dtype"] == "f32"
+    r = j["roofline"]
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9 and r["traffic"] > 0
+    e = j["e2e"]
+    assert e["value"] > 0 and e["h2d_bytes_per_step"] > 20e6 and e["d2h_bytes_per_step"] > 0 and e["value"] != j["value"]
+    assert j["gpu_launches"] == 6 * 16 and j["value"] > 0 and "workload" in j["config"]
+    assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(j["clocks"])
+    assert j["last_frame_abs_translation_error_m"] < 0.05   # the tracker pulls the 3 cm prior onto the ground truth
