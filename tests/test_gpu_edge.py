@@ -132,3 +132,35 @@ def test_depth_prefilter_bit_exact(torch_cuda, orc, synth, camname):
     d = to_dev(torch_cuda, raw)
     assert np.array_equal(filterDepth(d, maxD).cpu().numpy(), orc.depth_bilateral(raw, maxD))
     assert_f32_equal(metriciseDepth(d, maxD).cpu().numpy(), orc.depth_metric(raw, maxD), "metric depth")
+
+
+def test_oversubscribed_trackers_serialise_and_agree(torch_cuda, synth):
+    """More co-operative grids than the GPU can hold at once (3 x the full grid; mixed block sizes): the launches queue
+    instead of dead-locking at their grid barriers, and every tracker returns the same bits."""
+    import threading
+    from densemonoslam_b200.odometry import RGBDOdometry
+    cam = synth.scaled_camera(synth.CAM_VGA, 2)
+    model, live, T = synth.frame_pair(cam, seed=3)
+    D = {k: to_dev(torch_cuda, a) for k, a in (("v", model["vmap4"]), ("n", model["nmap4"]), ("mi", model["rgba"]), ("d", live["depth"]), ("li", live["rgba"]))}
+    pose = np.eye(4, dtype=np.float32)
+
+    def work(res, k, grid, threads):
+        h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
+        if threads:
+            h.set_block(threads)
+        h.set_grid(grid)
+        s = torch_cuda.cuda.Stream()
+        h.initFirstRGB(D["mi"], stream=s)
+        for _ in range(10):
+            h.initICPModel(D["v"], D["n"], 25.0, pose, stream=s); h.initRGBModel(D["mi"], stream=s); h.initICP(D["d"], 25.0, stream=s); h.initRGB(D["li"], stream=s)
+            t, R = h.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True, stream=s)
+        res[k] = (t, R, h.lastICPCount, h.lastRGBCount)
+
+    for cfgs in ([(0, 0)] * 3, [(0, 0), (148, 512), (60, 256), (0, 512)]):
+        res = {}
+        ths = [threading.Thread(target=work, args=(res, k, g, th)) for k, (g, th) in enumerate(cfgs)]
+        [t.start() for t in ths]
+        [t.join(timeout=120) for t in ths]
+        assert len(res) == len(cfgs), "a tracker did not finish"
+        for r in res.values():
+            assert np.array_equal(r[0], res[0][0]) and np.array_equal(r[1], res[0][1]) and r[2:] == res[0][2:]
