@@ -22,7 +22,8 @@ static const int ACC_SLOTS = 192;
 static const int MAX_TRACE = 160;   // >= 3*50 interMap iterations
 
 // Device-resident control block of the persistent tracking kernel.
-static const int SYNC_WORDS = 32 * 17;  // barrier words: arrive counter + 16 release-flag copies, one 128-byte line each
+static const int SYNC_WORDS = 32 * 19;  // barrier words: arrive counter + 16 release-flag copies + 2 work-list counters, one 128-byte line each
+static const int SYNC_LISTN = 32 * 17;  // sync[SYNC_LISTN + 32 * parity]: number of entries of the photometric segment list
 // Words of Ctrl::pub, the block the solver publishes for the workers' next phase (read once per CTA per barrier).
 enum { PUB_RCURR = 0, PUB_TCURR = 9, PUB_KRKINV = 12, PUB_KT = 21, PUB_SIGMA = 24, PUB_BRK = 25, PUB_SO3DONE = 26,
        PUB_SO3H = 27, PUB_SO3KINV = 36, PUB_SO3KRLR = 45, PUB_WORDS = 64 };
@@ -49,6 +50,7 @@ struct TrackParams {
   unsigned long long* acc;
   dms_iter_record* trace;
   int timing;
+  unsigned int* seglist;    // segments with at least one photometric term in the current iteration (any order), lv[0] segments long
   unsigned long long* dbg;  // timing mode: CTA 0 logs {tag, globaltimer} pairs here (MAX_DBG pairs)
 };
 static const int MAX_DBG = 1024;

@@ -26,6 +26,7 @@ struct dms_odom {
   dms_iter_record* trace;
   StepOut* step_out;
   unsigned long long* dbg;
+  unsigned int* seglist;
   unsigned char* mask;   // level-0 sized scratch for dms_odom_icp_step's inlier mask
   // staging for the *_host entry points (allocated on first use)
   float4 *stage_v4, *stage_n4; uchar4* stage_rgba; unsigned short* stage_depth;
@@ -162,6 +163,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   want((void**)&h->trace, sizeof(dms_iter_record) * MAX_TRACE);
   want((void**)&h->step_out, sizeof(StepOut));
   want((void**)&h->dbg, sizeof(unsigned long long) * 2 * MAX_DBG);
+  want((void**)&h->seglist, sizeof(unsigned int) * (size_t)h->lv[0].rows * ((h->lv[0].cols + 31) / 32));
   want((void**)&h->mask, (size_t)h->lv[0].rows * h->lv[0].pitch_u8);
   for (int r = 0; r < nreq; ++r) off += align_up(reqs[r].bytes, 256);
   h->slab_bytes = off;
@@ -363,6 +365,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   }
   P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = h->timing;
   P.dbg = h->timing ? h->dbg : nullptr;
+  P.seglist = h->seglist;
   if (h->timing) { CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s)); CK(cudaEventRecord(h->ev0, s)); }
   cudaError_t e = launch_track(P, h->grid, h->tpb, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
