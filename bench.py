@@ -208,6 +208,7 @@ def main():
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 1024)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wait", type=int, default=2, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep-then-poll")
     ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
     args = ap.parse_args()
 
@@ -279,6 +280,7 @@ def main():
                 h.set_block(threads)
             per_sm = max(1, 1024 // threads) if threads else 1
             h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // depth))
+            h.set_wait(args.wait if depth > 1 else 0)   # trackers sharing the GPU: do not burn a host core per tracker while waiting
             h.set_timing(True)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss

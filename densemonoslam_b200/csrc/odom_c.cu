@@ -5,6 +5,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sched.h>
+#include <chrono>
+#include <thread>
 #include <new>
 #include <string>
 #include "kernels.h"
@@ -38,6 +41,9 @@ struct dms_odom {
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
   cudaEvent_t ev0, ev1;
+  cudaEvent_t ev_done;   // blocking-sync event (dms_odom_set_wait): the host thread sleeps instead of spinning
+  int blocking_wait;     // 0 spin, 1 blocking-sync event, 2 sleep for most of the expected wait, then poll and yield
+  double wait_ema_us;    // running estimate of the wait (mode 2)
   std::string err;
 };
 
@@ -183,6 +189,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   }
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_done, cudaEventBlockingSync | cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dms_odom_destroy(h); return (int)e; }
   h->tpb = track_block_threads_max();
@@ -214,6 +221,7 @@ int dms_odom_destroy(dms_odom* h) {
   if (h->h_step) cudaFreeHost(h->h_step);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ev_done) cudaEventDestroy(h->ev_done);
   delete h;
   return DMS_OK;
 }
@@ -234,6 +242,7 @@ int dms_odom_set_block(dms_odom* h, int threads) {
   if (all || h->grid > g) h->grid = g;
   return DMS_OK;
 }
+int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 2) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
 int dms_odom_set_timing(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->timing = enabled ? 1 : 0; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 
@@ -371,6 +380,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
   if (h->timing) CK(cudaEventRecord(h->ev1, s));
   CK(cudaMemcpyAsync(h->h_ctrl, h->ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
+  if (h->blocking_wait) CK(cudaEventRecord(h->ev_done, s));
   if (so3)  // RO.cpp:595-601: the kernel holds the old pointers, so the swap can be applied right away
     for (int i = 0; i < 3; ++i) { unsigned char* t = h->lv[i].lastNextImage; h->lv[i].lastNextImage = h->lv[i].nextImage; h->lv[i].nextImage = t; }
   return DMS_OK;
@@ -379,7 +389,16 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
 int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stream, dms_odom_result* out) {
   if (!h || !trans || !rot) return fail(h, DMS_ERR_INVALID, "track_collect: null argument");
   Bind b(h->device);
-  cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  cudaError_t e;
+  if (h->blocking_wait == 2) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (h->wait_ema_us > 150.0) std::this_thread::sleep_for(std::chrono::nanoseconds((long long)(h->wait_ema_us * 850.0)));
+    while ((e = cudaEventQuery(h->ev_done)) == cudaErrorNotReady) sched_yield();
+    const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+    h->wait_ema_us = h->wait_ema_us == 0.0 ? us : 0.8 * h->wait_ema_us + 0.2 * us;
+  } else {
+    e = h->blocking_wait ? cudaEventSynchronize(h->ev_done) : cudaStreamSynchronize((cudaStream_t)stream);
+  }
   if (e != cudaSuccess) {
     // a failed launch leaves the barrier words undefined: rearm them
     memset(h->h_ctrl, 0, sizeof(Ctrl));

@@ -240,6 +240,10 @@ class RGBDOdometry:
         """Threads per block of the tracking kernel (0 = 1024); call before set_grid."""
         self._ck(self._L.dms_odom_set_block(self._h, int(threads)), "set_block")
 
+    def set_wait(self, mode=2):
+        """0 spin (default), 1 blocking-sync event, 2 sleep for most of the expected wait then poll and yield."""
+        self._ck(self._L.dms_odom_set_wait(self._h, int(mode)), "set_wait")
+
     def set_timing(self, enabled=True):
         self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")
 

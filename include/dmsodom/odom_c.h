@@ -78,6 +78,10 @@ int dms_odom_set_grid(dms_odom* h, int n_ctas);
  * more blocks (of different handles) are resident per SM, so one tracker's pixel phases fill the issue slots another
  * leaves idle at its barriers.  Resets the grid limit to "all" when it no longer fits.  Results do not depend on it. */
 int dms_odom_set_block(dms_odom* h, int threads);
+/* How dms_odom_track / dms_odom_track_collect wait for the result: 0 = spin on the stream (lowest latency, default),
+ * 1 = sleep on a blocking-sync event, 2 = sleep for 85 % of the running average of the last waits, then poll and yield
+ * (many trackers / ranks per host core without the wake-up latency of 1). */
+int dms_odom_set_wait(dms_odom* h, int mode);
 int dms_odom_set_timing(dms_odom* h, int enabled);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
 
