@@ -204,7 +204,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=8, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--pipeline", type=int, default=12, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 1024)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -279,7 +279,7 @@ def main():
             if threads:
                 h.set_block(threads)
             per_sm = max(1, 1024 // threads) if threads else 1
-            h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // depth))
+            h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // min(depth, 8)))  # at most 8 kernels resident; further trackers queue and take the slots as they free up
             h.set_wait(args.wait if depth > 1 else 0)   # trackers sharing the GPU: do not burn a host core per tracker while waiting
             h.set_timing(True)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
@@ -359,7 +359,8 @@ def main():
     def roofline_of(ms, steps, ktimes, iters_seen, so3_seen, depth):
         k_ms = float(np.mean(ktimes))
         alg = float(np.mean([algorithmic_bytes(cam, it, s3) for it, s3 in zip(iters_seen, so3_seen)]))
-        # `depth` tracking kernels run concurrently, each on 1/depth of the SMs: the aggregate rate is depth launches per k_ms
+        # `depth` = tracking kernels resident at once, each on its share of the block slots (further trackers queue): the
+        # aggregate rate of the kernel is depth launches per k_ms
         achieved = depth * alg / (k_ms * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": "k_track (persistent cooperative: derivatives + SO3 + 3-level GN incl. solves)", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
@@ -369,7 +370,7 @@ def main():
 
     depth = max(1, args.pipeline)
     _thr = args.threads if args.threads else 1024
-    _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // depth
+    _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, 8)
     config["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
                           if depth > 1 else "single tracker, frames strictly one after another")
     pipe = make_pipe(depth)
@@ -377,7 +378,7 @@ def main():
     value = world * args.steps / (ms * 1e-3)
     gt = frames[(args.steps - 1) % ring]["gt"]
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
-    roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, depth)
+    roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, 8) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
 
     if args.quick:
         emit({"value": value, "roofline": roofline, "config": config, "clocks": clocks})
