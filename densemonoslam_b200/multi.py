@@ -76,7 +76,7 @@ def _takes_cutoff(trk) -> bool:
 
 
 def _fields(trk, res):
-    if len(res) > 2:  # oracle stand-in returns (t, R, result struct)
+    if len(res) > 2:  # a tracker stand-in injected by the CPU tests returns (t, R, result struct)
         r = res[2]
         return [r.lastICPError, r.lastICPCount, r.lastRGBError, r.lastRGBCount, r.lastSO3Error, r.lastSO3Count]
     return [trk.lastICPError, trk.lastICPCount, trk.lastRGBError, trk.lastRGBCount, trk.lastSO3Error, trk.lastSO3Count]

@@ -1,7 +1,8 @@
-"""Device timings (CUDA events, inputs resident) of the SURVEY 8f "next" rows beside their CPU restatements:
+"""(lives under tests/ because it times the CPU restatements of oracle/ beside the kernels)
+Device timings (CUDA events, inputs resident) of the SURVEY 8f "next" rows beside their CPU restatements:
 depth pre-filter (N2), FillIn / denseEnough (N1), surfel-splat prediction (N3), NID score (N4)."""
 import json, os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
 import torch
 from densemonoslam_b200 import synth, splat, frontend
