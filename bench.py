@@ -209,6 +209,7 @@ def main():
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wait", type=int, default=2, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep-then-poll")
+    ap.add_argument("--no-share-rgb", action="store_true", help="pipelined trackers reload the previous frame's image instead of taking its pyramid from the tracker that has it")
     ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
     args = ap.parse_args()
 
@@ -268,6 +269,8 @@ def main():
     props = torch.cuda.get_device_properties(local_rank)
     sms = props.multi_processor_count
 
+    share_rgb = not args.no_share_rgb
+
     def make_pipe(depth):
         """`depth` trackers sharing the GPU (SMs split evenly), each on its own stream.  Frame f goes to tracker
         f % depth; before it, the tracker's SO(3) reference image is (re)loaded from frame f-1 (initFirstRGB), so the
@@ -285,17 +288,32 @@ def main():
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss
 
-    def one_frame(h, st, i, host):
+    def one_frame(h, st, i, host, prev_tracker=None, sync=None):
+        """One tracked frame.  The SO(3) reference image of frame i is the live image of frame i-1: with one tracker it is
+        already in place (RO.cpp:595-601); with trackers taking turns it comes from the pyramid of the tracker that
+        processed frame i-1 (`prev_tracker`, dms_odom_init_first_rgb_from), or is loaded again when that is not possible
+        (first frame of a run)."""
         f = frames[i % ring]
         src = pinned if host else dev
         cur, prev = src[i % ring], src[(i - 1) % ring]
         get = (lambda t: t.numpy()) if host else (lambda t: t)
         p = f["prior"]
-        h.initFirstRGB(get(prev["li"]), stream=st)
         h.initICPModel(get(cur["v"]), get(cur["n"]), 25.0, p, stream=st)
         h.initRGBModel(get(cur["mi"]), stream=st)
         h.initICP(get(cur["d"]), 25.0, stream=st)
+        if sync is not None:
+            sync["taken"][i].wait()      # the frame that takes this tracker's previous image has issued its copy
         h.initRGB(get(cur["li"]), stream=st)
+        if sync is not None:
+            sync["issued"][i].set()
+        if prev_tracker is not None:
+            sync["issued"][i - 1].wait()  # frame i-1's initRGB call has returned
+            h.initFirstRGBFrom(prev_tracker, stream=st)
+            sync["taken"][i - 1 + len(sync["hs"])].set()
+        else:
+            h.initFirstRGB(get(prev["li"]), stream=st)
+            if sync is not None:
+                sync["taken"][i - 1 + len(sync["hs"])].set()
         return h.getIncrementalTransformation(p[:3, 3], p[:3, :3], FLAGS["rgbOnly"], FLAGS["icpWeight"], FLAGS["pyramid"], FLAGS["fastOdom"],
                                               FLAGS["so3"], stream=st)
 
@@ -316,11 +334,19 @@ def main():
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         stats = [{"k": [], "it": [], "so3": [], "last": None, "lat": [], "phase": []} for _ in range(depth)]
 
+        # host-side ordering between the trackers' threads: issued[i] = initRGB of frame i has returned; taken[j] = the
+        # image tracker j % depth holds from frame j - depth has been handed on, so frame j may load its own
+        sync = None
+        if depth > 1 and share_rgb:
+            sync = {"hs": hs, "issued": [threading.Event() for _ in range(steps + 1)], "taken": [threading.Event() for _ in range(steps + depth + 1)]}
+            for j in range(depth):
+                sync["taken"][j].set()   # the first frame of every tracker has nothing to wait for
+
         def work(k):
             torch.cuda.set_device(local_rank)
             for i in range(k, steps, depth):
                 t_host = time.perf_counter()
-                out = one_frame(hs[k], ss[k], i, host)
+                out = one_frame(hs[k], ss[k], i, host, hs[(i - 1) % depth] if (sync is not None and i > 0) else None, sync)
                 stats[k]["lat"].append((time.perf_counter() - t_host) * 1e3)   # host-visible latency of one frame (result in hand)
                 tm = hs[k].timing()
                 stats[k]["k"].append(tm["track"]); stats[k]["it"].append(list(hs[k].iters)); stats[k]["so3"].append(hs[k].so3_iters)
@@ -390,10 +416,10 @@ def main():
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": config, "roofline": roofline,
-           "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + frames[0]["live"]["rgba"].nbytes,
+           "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + (0 if (share_rgb and depth > 1) else frames[0]["live"]["rgba"].nbytes),
                    "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
-           "gpu_launches": 6 * args.steps,  # per frame: k_populate x3, k_maps_pyramid, k_icp_depth, k_track (profiles/r01_launches_kitti_final.csv)
+           "gpu_launches": (5 * args.steps + 1) if (share_rgb and depth > 1) else 6 * args.steps,  # per frame: k_populate x2 (x3 when the previous image is reloaded), k_maps_pyramid, k_icp_depth, k_track
            "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
            "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
     if world > 1:

@@ -79,6 +79,7 @@ SIGNATURES = {
     "dms_odom_init_rgb": (C.c_int, [_P, _P, C.c_size_t, _P]),
     "dms_odom_init_rgb_model": (C.c_int, [_P, _P, C.c_size_t, _P]),
     "dms_odom_init_first_rgb": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "dms_odom_init_first_rgb_from": (C.c_int, [_P, _P, _P]),
     "dms_odom_init_icp_depth_host": (C.c_int, [_P, _P, C.c_size_t, C.c_float, _P]),
     "dms_odom_init_icp_maps_host": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _P]),
     "dms_odom_init_icp_model_host": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_float, _F3, _P]),

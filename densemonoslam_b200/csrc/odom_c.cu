@@ -41,6 +41,8 @@ struct dms_odom {
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
   cudaEvent_t ev0, ev1;
+  cudaEvent_t ev_rgb;    // recorded after every initRGB: the intensity pyramid in rgb_pyr[] is complete (init_first_rgb_from waits on it)
+  unsigned char* rgb_pyr[3];  // memory that received the image of the last initRGB (stable across the nextImage / lastNextImage pointer swap)
   cudaEvent_t ev_done;   // blocking-sync event (dms_odom_set_wait): the host thread sleeps instead of spinning
   int blocking_wait;     // 0 spin, 1 blocking-sync event, 2 sleep for most of the expected wait, then poll and yield
   double wait_ema_us;    // running estimate of the wait (mode 2)
@@ -189,6 +191,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   }
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_rgb, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_done, cudaEventBlockingSync | cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dms_odom_destroy(h); return (int)e; }
@@ -222,6 +225,7 @@ int dms_odom_destroy(dms_odom* h) {
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev_done) cudaEventDestroy(h->ev_done);
+  if (h->ev_rgb) cudaEventDestroy(h->ev_rgb);
   delete h;
   return DMS_OK;
 }
@@ -280,7 +284,11 @@ int dms_odom_init_icp_model(dms_odom* h, const float* d_v4, const float* d_n4, s
 int dms_odom_init_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch, void* stream) {
   if (!h || !d_rgba) return fail(h, DMS_ERR_INVALID, "init_rgb: null argument");
   Bind b(h->device);
-  return populate(h, d_rgba, pitch ? pitch : (size_t)h->width * 4, 1, (cudaStream_t)stream);
+  const int rc = populate(h, d_rgba, pitch ? pitch : (size_t)h->width * 4, 1, (cudaStream_t)stream);
+  if (rc != DMS_OK) return rc;
+  for (int i = 0; i < 3; ++i) h->rgb_pyr[i] = h->lv[i].nextImage;
+  CK(cudaEventRecord(h->ev_rgb, (cudaStream_t)stream));
+  return DMS_OK;
 }
 int dms_odom_init_rgb_model(dms_odom* h, const uint8_t* d_rgba, size_t pitch, void* stream) {
   if (!h || !d_rgba) return fail(h, DMS_ERR_INVALID, "init_rgb_model: null argument");
@@ -291,6 +299,20 @@ int dms_odom_init_first_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch, vo
   if (!h || !d_rgba) return fail(h, DMS_ERR_INVALID, "init_first_rgb: null argument");
   Bind b(h->device);
   return populate(h, d_rgba, pitch ? pitch : (size_t)h->width * 4, 2, (cudaStream_t)stream);
+}
+
+int dms_odom_init_first_rgb_from(dms_odom* h, const dms_odom* src, void* stream) {
+  if (!h || !src || src == h) return fail(h, DMS_ERR_INVALID, "init_first_rgb_from: bad argument");
+  if (src->device != h->device || src->width != h->width || src->height != h->height || !src->rgb_pyr[0])
+    return fail(h, DMS_ERR_INVALID, "init_first_rgb_from: source has another size / device or no image yet");
+  Bind b(h->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(cudaStreamWaitEvent(s, src->ev_rgb, 0));
+  for (int i = 0; i < 3; ++i) {
+    const Level& L = h->lv[i];
+    CK(cudaMemcpy2DAsync(L.lastNextImage, L.pitch_u8, src->rgb_pyr[i], src->lv[i].pitch_u8, (size_t)L.cols, (size_t)L.rows, cudaMemcpyDeviceToDevice, s));
+  }
+  return DMS_OK;
 }
 
 // ---- host-buffer variants

@@ -136,6 +136,10 @@ class RGBDOdometry:
     def initFirstRGB(self, rgb, stream=None):
         self._rgb(rgb, self._L.dms_odom_init_first_rgb, self._L.dms_odom_init_first_rgb_host, "initFirstRGB", stream)
 
+    def initFirstRGBFrom(self, src, stream=None):
+        """initFirstRGB with the image of `src`'s last initRGB, copied from its pyramid on the device (dms_odom_init_first_rgb_from)."""
+        self._ck(self._L.dms_odom_init_first_rgb_from(self._h, src._h, self._stream(stream)), "initFirstRGBFrom")
+
     def _take(self, res):
         self.lastICPError, self.lastICPCount = res.lastICPError, res.lastICPCount
         self.lastRGBError, self.lastRGBCount = res.lastRGBError, res.lastRGBCount

@@ -102,6 +102,14 @@ int dms_odom_init_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, vo
 int dms_odom_init_rgb_model(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, void* stream);
 int dms_odom_init_first_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch_bytes, void* stream);
 
+/* initFirstRGB with the image `src` received in its most recent initRGB call, taken from src's pyramid on the device
+ * (three small device-to-device copies instead of a conversion + two pyrDowns, and no re-upload from the host).  For
+ * trackers that take turns on the frames of one sequence: tracker k gets frame f-1 from the tracker that processed it.
+ * Ordered after src's initRGB by an event; the caller makes sure that call has RETURNED, and that src does not start
+ * its initRGB after next before this copy has run (the image stays in place for one full frame of src).  No reference
+ * counterpart (the reference has one tracker per sensor). */
+int dms_odom_init_first_rgb_from(dms_odom* h, const dms_odom* src, void* stream);
+
 /* Same five calls with HOST buffers (dense rows unless pitch given); the copy to the device
  * is part of the call.  Used by callers without a device-side producer and by bench.py's
  * end-to-end number. */

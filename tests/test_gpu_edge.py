@@ -164,3 +164,29 @@ def test_oversubscribed_trackers_serialise_and_agree(torch_cuda, synth):
         assert len(res) == len(cfgs), "a tracker did not finish"
         for r in res.values():
             assert np.array_equal(r[0], res[0][0]) and np.array_equal(r[1], res[0][1]) and r[2:] == res[0][2:]
+
+
+def test_first_rgb_from_another_tracker(torch_cuda, synth):
+    """dms_odom_init_first_rgb_from: the SO(3) reference image taken from the pyramid of the tracker that processed the
+    previous frame gives the same track, bit for bit, as loading that image with initFirstRGB."""
+    from densemonoslam_b200.odometry import RGBDOdometry
+    cam = synth.scaled_camera(synth.CAM_VGA, 2)
+    m0, l0, _ = synth.frame_pair(cam, seed=5)
+    m1, l1, _ = synth.frame_pair(cam, seed=6, rvec=(0.004, 0.002, -0.003), tvec=(0.006, 0.004, -0.002))
+    pose = np.eye(4, dtype=np.float32)
+    d = lambda a: to_dev(torch_cuda, a)
+
+    def frame(h, m, l):
+        h.initICPModel(d(m["vmap4"]), d(m["nmap4"]), 25.0, pose); h.initRGBModel(d(m["rgba"])); h.initICP(d(l["depth"]), 25.0); h.initRGB(d(l["rgba"]))
+
+    a, b, c = (RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy) for _ in range(3))
+    # tracker a processes frame 0 (and tracks, which swaps its image pyramids); b and c process frame 1
+    a.initFirstRGB(d(m0["rgba"])); frame(a, m0, l0)
+    a.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
+    frame(b, m1, l1); b.initFirstRGBFrom(a)
+    frame(c, m1, l1); c.initFirstRGB(d(l0["rgba"]))
+    assert np.array_equal(b.download("lastNextImage", 0), c.download("lastNextImage", 0))
+    assert np.array_equal(b.download("lastNextImage", 2), c.download("lastNextImage", 2))
+    tb, Rb = b.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
+    tc, Rc = c.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
+    assert np.array_equal(tb, tc) and np.array_equal(Rb, Rc) and b.lastSO3Count == c.lastSO3Count
