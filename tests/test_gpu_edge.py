@@ -190,3 +190,19 @@ def test_first_rgb_from_another_tracker(torch_cuda, synth):
     tb, Rb = b.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
     tc, Rc = c.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], False, 10.0, True, False, True)
     assert np.array_equal(tb, tc) and np.array_equal(Rb, Rc) and b.lastSO3Count == c.lastSO3Count
+
+
+@pytest.mark.parametrize("grid,threads", [(8, 512), (37, 512), (5, 1024)])
+def test_full_track_parity_in_the_shared_gpu_launch_shape(torch_cuda, orc, synth, grid, threads):
+    """The launch shapes trackers use when they share the GPU (few blocks, 512 threads): every warp walks many segments and
+    phase B takes the photometric work list (sparse terms) -- integer outputs bit-exact at every iteration, as with the
+    full grid."""
+    cam = synth.CAM_KITTI
+    frames = synth.kitti_sequence(cam, 2, seed=2021)
+    g, o = both(orc, synth, cam)
+    g.set_block(threads); g.set_grid(grid)
+    g.initFirstRGB(to_dev(torch_cuda, frames[0]["live"]["rgba"])); o.initFirstRGB(frames[0]["live"]["rgba"])
+    for f in frames:
+        prior = f["prior"]
+        load_frame_to_model(torch_cuda, g, o, f["model"], f["live"], prior)
+        compare_track(g, o, prior[:3, 3].copy(), prior[:3, :3].copy(), FLAG_ROWS["frameToModel"])
