@@ -209,6 +209,7 @@ def main():
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wait", type=int, default=2, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep-then-poll")
+    ap.add_argument("--driver", default="native", choices=["native", "python"], help="who runs the trackers' host threads when they share the GPU: the library's sequence runner or Python threads")
     ap.add_argument("--no-share-rgb", action="store_true", help="pipelined trackers reload the previous frame's image instead of taking its pyramid from the tracker that has it")
     ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
     args = ap.parse_args()
@@ -323,6 +324,39 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed_native(seq, steps, warmup, host):
+        """The same timed region through the library's own sequence runner (dms_sequence_run): the trackers' host threads
+        live in C++, so the interpreter lock is not on the path."""
+        src = pinned if host else dev
+
+        def frame_list(n):
+            return [{"v": src[i % ring]["v"], "n": src[i % ring]["n"], "mi": src[i % ring]["mi"], "d": src[i % ring]["d"], "li": src[i % ring]["li"],
+                     "prior": frames[i % ring]["prior"]} for i in range(n)]
+        first_prev = src[(0 - 1) % ring]["li"]
+        seq.run(seq.make_frames(frame_list(max(3, warmup) * max(1, seq.options.n_trackers))), first_prev, host)
+        fc = seq.make_frames(frame_list(steps))
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        res = seq.run(fc, first_prev, host)
+        torch.cuda.synchronize()
+        ev1.record()
+        barrier()
+        ms = ev0.elapsed_time(ev1)
+        clocks = sampler.result()
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        ktimes = [r.track_ms for r in res]
+        iters_seen = [list(r.r.iters) for r in res]
+        so3_seen = [r.r.so3_iters for r in res]
+        pose = np.array(res[steps - 1].pose[:], np.float32).reshape(4, 4)
+        timed_native.last_result = res[steps - 1].r
+        return ms, ktimes, iters_seen, so3_seen, clocks, (pose[:3, 3].copy(), pose[:3, :3].copy())
+
     def timed(pipe, steps, warmup, host):
         hs, ss = pipe
         depth = len(hs)
@@ -399,8 +433,20 @@ def main():
     _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, 8)
     config["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
                           if depth > 1 else "single tracker, frames strictly one after another")
-    pipe = make_pipe(depth)
-    ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
+    native = depth > 1 and args.driver == "native" and share_rgb
+    seq = None
+    if native:
+        from densemonoslam_b200.sequence import SequenceTracker
+        seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth, block_threads=args.threads,
+                              grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
+                              fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0)
+        config["driver"] = "dms_sequence_run (native host threads)"
+        pipe = None
+        ms, ktimes, iters_seen, so3_seen, clocks, last = timed_native(seq, args.steps, args.warmup, False)
+    else:
+        config["driver"] = "python threads over the per-call C ABI"
+        pipe = make_pipe(depth)
+        ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
     value = world * args.steps / (ms * 1e-3)
     gt = frames[(args.steps - 1) % ring]["gt"]
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
@@ -410,7 +456,7 @@ def main():
         emit({"value": value, "roofline": roofline, "config": config, "clocks": clocks})
         return
     e2e_steps = min(args.steps, 300)
-    ms_e2e, _, _, _, _, _ = timed(pipe, e2e_steps, min(args.warmup, 5), True)
+    ms_e2e, _, _, _, _, _ = timed_native(seq, e2e_steps, min(args.warmup, 5), True) if native else timed(pipe, e2e_steps, min(args.warmup, 5), True)
     e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
 
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -425,14 +471,14 @@ def main():
     if world > 1:
         # the only exchange of the multi-sensor mode: per-frame result records, gathered on rank 0 outside the timed region
         from densemonoslam_b200 import multi
-        rec = multi.pack_record(last[0], last[1], [pipe[0][0].lastICPError, pipe[0][0].lastICPCount, pipe[0][0].lastRGBError,
-                                                   pipe[0][0].lastRGBCount, pipe[0][0].lastSO3Error, pipe[0][0].lastSO3Count])
+        lr = timed_native.last_result if native else pipe[0][0]
+        rec = multi.pack_record(last[0], last[1], [lr.lastICPError, lr.lastICPCount, lr.lastRGBError, lr.lastRGBCount, lr.lastSO3Error, lr.lastSO3Count])
         full = multi.gather_records({rank: rec[None]}, world, 1, device="cuda")
         if rank == 0:
             out["gathered_result_records"] = list(full.shape)
     if depth > 1 and world == 1:
         # the same sequence on one tracker owning the whole GPU: per-frame latency and the full-GPU kernel roofline
-        del pipe
+        del pipe, seq
         pipe1 = make_pipe(1)
         ms1, k1, it1, s31, _, _ = timed(pipe1, min(args.steps, 300), args.warmup, False)
         n1 = min(args.steps, 300)

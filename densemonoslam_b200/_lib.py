@@ -58,6 +58,20 @@ class DmsSplatParams(C.Structure):
                 ("maxTime", C.c_int), ("timeDelta", C.c_int), ("active", C.c_int)]
 
 
+class DmsSeqFrame(C.Structure):
+    _fields_ = [("vertex4", C.c_void_p), ("normal4", C.c_void_p), ("model_rgba", C.c_void_p), ("depth", C.c_void_p), ("live_rgba", C.c_void_p),
+                ("prior", C.c_float * 16)]
+
+
+class DmsSeqResult(C.Structure):
+    _fields_ = [("pose", C.c_float * 16), ("r", DmsResult), ("track_ms", C.c_float)]
+
+
+class DmsSeqOptions(C.Structure):
+    _fields_ = [("n_trackers", C.c_int), ("block_threads", C.c_int), ("grid", C.c_int), ("wait_mode", C.c_int), ("rgbOnly", C.c_int),
+                ("icpWeight", C.c_float), ("pyramid", C.c_int), ("fastOdom", C.c_int), ("so3", C.c_int), ("depthCutoff", C.c_float)]
+
+
 # int (*dms_predict_fn)(void* user, const float pose[16], int kind, int tick, void* stream, dms_model_view* out)
 PREDICT_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_int, C.c_void_p, C.POINTER(DmsModelView))
 
@@ -127,6 +141,11 @@ SIGNATURES = {
     "dms_nid_depth": (C.c_int, [_P, _P, _P, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_float, _P, _P, _F3, _P]),
     "dms_splat_predict": (C.c_int, [_P, C.c_int, C.POINTER(DmsSplatParams), _P, _P, _P, _P, _P, _P]),
     "dms_splat_invert_pose": (C.c_int, [_F3, _F3]),
+    "dms_sequence_default_options": (None, [C.POINTER(DmsSeqOptions)]),
+    "dms_sequence_create": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int] + [C.c_float] * 4 + [C.POINTER(DmsSeqOptions)]),
+    "dms_sequence_destroy": (C.c_int, [_P]),
+    "dms_sequence_run": (C.c_int, [_P, C.POINTER(DmsSeqFrame), C.c_int, _P, C.c_int, C.POINTER(DmsSeqResult)]),
+    "dms_sequence_resident": (C.c_int, [_P]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

@@ -41,6 +41,8 @@ struct dms_odom {
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
   cudaEvent_t ev0, ev1;
+  cudaEvent_t ev_took;   // recorded after this handle copied another tracker's pyramid (init_first_rgb_from)
+  cudaEvent_t wait_reader;  // ev_took of the tracker that is reading rgb_pyr[]: the next write to an image pyramid waits for it
   cudaEvent_t ev_rgb;    // recorded after every initRGB: the intensity pyramid in rgb_pyr[] is complete (init_first_rgb_from waits on it)
   unsigned char* rgb_pyr[3];  // memory that received the image of the last initRGB (stable across the nextImage / lastNextImage pointer swap)
   cudaEvent_t ev_done;   // blocking-sync event (dms_odom_set_wait): the host thread sleeps instead of spinning
@@ -89,6 +91,10 @@ void mat3_inv_host(const T* m, T* o) {  // same operation order as the oracle's 
 
 int populate(dms_odom* h, const uint8_t* d_rgba, size_t pitch, int which, cudaStream_t s) {
   // which: 0 = last (initRGBModel), 1 = next (initRGB), 2 = lastNext image only (initFirstRGB)
+  if (which != 0 && h->wait_reader) {  // another tracker may still be copying the image this call overwrites
+    CK(cudaStreamWaitEvent(s, h->wait_reader, 0));
+    h->wait_reader = nullptr;
+  }
   CK(launch_populate(h->lv, which, h->zdepth, reinterpret_cast<const uchar4*>(d_rgba), (int)pitch, s));
   return DMS_OK;
 }
@@ -192,6 +198,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
   if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_rgb, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_took, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_done, cudaEventBlockingSync | cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dms_odom_destroy(h); return (int)e; }
@@ -226,6 +233,7 @@ int dms_odom_destroy(dms_odom* h) {
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev_done) cudaEventDestroy(h->ev_done);
   if (h->ev_rgb) cudaEventDestroy(h->ev_rgb);
+  if (h->ev_took) cudaEventDestroy(h->ev_took);
   delete h;
   return DMS_OK;
 }
@@ -307,11 +315,15 @@ int dms_odom_init_first_rgb_from(dms_odom* h, const dms_odom* src, void* stream)
     return fail(h, DMS_ERR_INVALID, "init_first_rgb_from: source has another size / device or no image yet");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
+  if (h->wait_reader) { CK(cudaStreamWaitEvent(s, h->wait_reader, 0)); h->wait_reader = nullptr; }
   CK(cudaStreamWaitEvent(s, src->ev_rgb, 0));
   for (int i = 0; i < 3; ++i) {
     const Level& L = h->lv[i];
     CK(cudaMemcpy2DAsync(L.lastNextImage, L.pitch_u8, src->rgb_pyr[i], src->lv[i].pitch_u8, (size_t)L.cols, (size_t)L.rows, cudaMemcpyDeviceToDevice, s));
   }
+  // src's next write to that memory (its own initFirstRGB / initRGB, possibly on another stream) has to wait for these copies
+  CK(cudaEventRecord(h->ev_took, s));
+  const_cast<dms_odom*>(src)->wait_reader = h->ev_took;
   return DMS_OK;
 }
 

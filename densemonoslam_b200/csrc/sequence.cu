@@ -1,0 +1,152 @@
+// Sequence runner (include/dmsodom/sequence_c.h): K trackers take turns on the frames of one open-loop sequence, one host
+// thread and one stream each.  Host-side ordering between the threads (per frame):
+//   issued[i]  initRGB of frame i has returned (its pyramid may be taken by frame i + 1)
+//   taken[j]   the image tracker j % K holds from frame j - K has been handed on, frame j may load its own
+#include <string.h>
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <new>
+#include <thread>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/dmsodom/sequence_c.h"
+
+namespace {
+
+struct Flags {  // monotone per-frame flags, waited on by other threads
+  std::mutex m; std::condition_variable cv; std::vector<char> f;
+  void reset(size_t n) { std::lock_guard<std::mutex> l(m); f.assign(n, 0); }
+  void set(size_t i) { { std::lock_guard<std::mutex> l(m); f[i] = 1; } cv.notify_all(); }
+  void wait(size_t i, const std::atomic<int>& err) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return f[i] || err.load(); }); }
+  void wake() { cv.notify_all(); }
+};
+
+}  // namespace
+
+struct dms_sequence {
+  int device, width, height;
+  dms_seq_options opt;
+  std::vector<dms_odom*> trk;
+  std::vector<cudaStream_t> streams;
+  int grid, resident;
+  Flags issued, taken;
+};
+
+extern "C" {
+
+void dms_sequence_default_options(dms_seq_options* o) {
+  if (!o) return;
+  o->n_trackers = 12; o->block_threads = 512; o->grid = 0; o->wait_mode = 2;
+  o->rgbOnly = 0; o->icpWeight = 10.0f; o->pyramid = 1; o->fastOdom = 0; o->so3 = 1; o->depthCutoff = 25.0f;
+}
+
+int dms_sequence_destroy(dms_sequence* s) {
+  if (!s) return DMS_OK;
+  cudaSetDevice(s->device);
+  for (size_t i = 0; i < s->trk.size(); ++i) if (s->trk[i]) dms_odom_destroy(s->trk[i]);
+  for (size_t i = 0; i < s->streams.size(); ++i) if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
+  delete s;
+  return DMS_OK;
+}
+
+int dms_sequence_create(dms_sequence** out, int device, int width, int height, float cx, float cy, float fx, float fy, const dms_seq_options* opt) {
+  if (!out) return DMS_ERR_INVALID;
+  *out = nullptr;
+  dms_seq_options o;
+  if (opt) o = *opt; else dms_sequence_default_options(&o);
+  if (o.n_trackers < 1 || o.n_trackers > 64) return DMS_ERR_INVALID;
+  dms_sequence* s = new (std::nothrow) dms_sequence();
+  if (!s) return DMS_ERR_NOMEM;
+  s->device = device; s->width = width; s->height = height; s->opt = o; s->grid = 0; s->resident = 1;
+  cudaSetDevice(device);
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const float angle = sinf(20.f * 3.14159254f / 180.f);
+  for (int k = 0; k < o.n_trackers; ++k) {
+    dms_odom* h = nullptr;
+    int rc = dms_odom_create(&h, device, width, height, cx, cy, fx, fy, 0.10f, angle);
+    if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; }
+    s->trk.push_back(h);
+    cudaStream_t st = nullptr;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { dms_sequence_destroy(s); return DMS_ERR_DEVICE; }
+    s->streams.push_back(st);
+    if (o.n_trackers > 1) {
+      const int threads = o.block_threads > 0 ? o.block_threads : 1024;
+      if (o.block_threads > 0) { rc = dms_odom_set_block(h, o.block_threads); if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; } }
+      const int slots = sms * (1024 / threads > 0 ? 1024 / threads : 1);
+      s->grid = o.grid > 0 ? o.grid : slots / (o.n_trackers < 8 ? o.n_trackers : 8);
+      dms_odom_set_grid(h, s->grid);
+      s->resident = slots / s->grid < o.n_trackers ? slots / s->grid : o.n_trackers;
+      dms_odom_set_wait(h, o.wait_mode);
+    }
+    dms_odom_set_timing(h, 1);
+  }
+  *out = s;
+  return DMS_OK;
+}
+
+int dms_sequence_resident(const dms_sequence* s) { return s ? s->resident : 0; }
+
+int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const uint8_t* first_prev, int host, dms_seq_result* out) {
+  if (!s || !frames || !out || n < 0 || (n > 0 && !first_prev)) return DMS_ERR_INVALID;
+  const int K = (int)s->trk.size();
+  const dms_seq_options& o = s->opt;
+  s->issued.reset((size_t)n + 1);
+  s->taken.reset((size_t)n + K + 1);
+  for (int j = 0; j < K; ++j) s->taken.set((size_t)j);
+  std::atomic<int> err(0);
+  auto work = [&](int k) {
+    cudaSetDevice(s->device);
+    dms_odom* h = s->trk[k];
+    void* st = (void*)s->streams[k];
+    for (int i = k; i < n && !err.load(); i += K) {
+      const dms_seq_frame& f = frames[i];
+      int rc;
+      if (host) {
+        rc = dms_odom_init_icp_model_host(h, f.vertex4, f.normal4, 0, o.depthCutoff, f.prior, st);
+        if (!rc) rc = dms_odom_init_rgb_model_host(h, f.model_rgba, 0, st);
+        if (!rc) rc = dms_odom_init_icp_depth_host(h, f.depth, 0, o.depthCutoff, st);
+      } else {
+        rc = dms_odom_init_icp_model(h, f.vertex4, f.normal4, 0, o.depthCutoff, f.prior, st);
+        if (!rc) rc = dms_odom_init_rgb_model(h, f.model_rgba, 0, st);
+        if (!rc) rc = dms_odom_init_icp_depth(h, f.depth, 0, o.depthCutoff, st);
+      }
+      if (!rc) {
+        if (K > 1) s->taken.wait((size_t)i, err);
+        rc = host ? dms_odom_init_rgb_host(h, f.live_rgba, 0, st) : dms_odom_init_rgb(h, f.live_rgba, 0, st);
+      }
+      s->issued.set((size_t)i);
+      if (!rc) {
+        if (i == 0 || K == 1) {
+          // one tracker keeps its own previous image (RO.cpp:595-601); the first frame loads the one it is given
+          if (i == 0) rc = host ? dms_odom_init_first_rgb_host(h, first_prev, 0, st) : dms_odom_init_first_rgb(h, first_prev, 0, st);
+        } else {
+          s->issued.wait((size_t)i - 1, err);
+          if (!err.load()) rc = dms_odom_init_first_rgb_from(h, s->trk[(i - 1) % K], st);
+        }
+      }
+      s->taken.set((size_t)i - 1 + K);
+      float trans[3] = {f.prior[3], f.prior[7], f.prior[11]};
+      float rot[9] = {f.prior[0], f.prior[1], f.prior[2], f.prior[4], f.prior[5], f.prior[6], f.prior[8], f.prior[9], f.prior[10]};
+      if (!rc) rc = dms_odom_track(h, trans, rot, o.rgbOnly, o.icpWeight, o.pyramid, o.fastOdom, o.so3, 0, st, &out[i].r);
+      if (rc) { err.store(rc); s->issued.wake(); s->taken.wake(); break; }
+      float* p = out[i].pose;
+      for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) p[r * 4 + c] = rot[r * 3 + c]; p[r * 4 + 3] = trans[r]; }
+      p[12] = p[13] = p[14] = 0.f; p[15] = 1.f;
+      dms_odom_timing tm;
+      dms_odom_get_timing(h, &tm);
+      out[i].track_ms = tm.track_ms;
+    }
+  };
+  if (K == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int k = 0; k < K; ++k) th.emplace_back(work, k);
+    for (auto& t : th) t.join();
+  }
+  return err.load();
+}
+
+}  // extern "C"

@@ -105,9 +105,10 @@ int dms_odom_init_first_rgb(dms_odom* h, const uint8_t* d_rgba, size_t pitch_byt
 /* initFirstRGB with the image `src` received in its most recent initRGB call, taken from src's pyramid on the device
  * (three small device-to-device copies instead of a conversion + two pyrDowns, and no re-upload from the host).  For
  * trackers that take turns on the frames of one sequence: tracker k gets frame f-1 from the tracker that processed it.
- * Ordered after src's initRGB by an event; the caller makes sure that call has RETURNED, and that src does not start
- * its initRGB after next before this copy has run (the image stays in place for one full frame of src).  No reference
- * counterpart (the reference has one tracker per sensor). */
+ * On the device the copy is ordered after src's initRGB and before src's next write to that memory by events.  On the
+ * host the caller orders the calls: src's initRGB has RETURNED before this call, and this call has returned before src's
+ * next initRGB / initFirstRGB* call starts (dms_sequence_run does both).  No reference counterpart (the reference has one
+ * tracker per sensor). */
 int dms_odom_init_first_rgb_from(dms_odom* h, const dms_odom* src, void* stream);
 
 /* Same five calls with HOST buffers (dense rows unless pitch given); the copy to the device

@@ -8,7 +8,7 @@ import pytest
 
 from conftest import ROOT
 
-HEADERS = [os.path.join(ROOT, "include", "dmsodom", n) for n in ("odom_c.h", "frontend_c.h", "nid_c.h", "splat_c.h")]
+HEADERS = [os.path.join(ROOT, "include", "dmsodom", n) for n in ("odom_c.h", "frontend_c.h", "nid_c.h", "splat_c.h", "sequence_c.h")]
 
 
 def declared_symbols():
@@ -68,7 +68,7 @@ def test_create_fails_loudly_without_gpu():
 def test_headers_compile_as_c_and_cpp(tmp_path):
     """The four C-ABI headers are plain C (and valid C++): no torch / CUDA types in the signatures."""
     inc = os.path.join(ROOT, "include")
-    src = '#include "dmsodom/odom_c.h"\n#include "dmsodom/frontend_c.h"\n#include "dmsodom/splat_c.h"\n#include "dmsodom/nid_c.h"\nint main(void) { return 0; }\n'
+    src = '#include "dmsodom/odom_c.h"\n#include "dmsodom/frontend_c.h"\n#include "dmsodom/splat_c.h"\n#include "dmsodom/nid_c.h"\n#include "dmsodom/sequence_c.h"\nint main(void) { return 0; }\n'
     for comp, name, std in (("gcc", "t.c", "-std=c99"), ("g++", "t.cpp", "-std=c++11")):
         f = tmp_path / name
         f.write_text(src)
