@@ -456,14 +456,15 @@ def main():
         emit({"value": value, "roofline": roofline, "config": config, "clocks": clocks})
         return
     e2e_steps = min(args.steps, 300)
-    ms_e2e, _, _, _, _, _ = timed_native(seq, e2e_steps, min(args.warmup, 5), True) if native else timed(pipe, e2e_steps, min(args.warmup, 5), True)
+    ms_e2e, _, _, _, _, last_e2e = timed_native(seq, e2e_steps, min(args.warmup, 5), True) if native else timed(pipe, e2e_steps, min(args.warmup, 5), True)
+    pose_err_e2e = float(np.max(np.abs(last_e2e[0] - frames[(e2e_steps - 1) % ring]["gt"][:3, 3])))
     e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
 
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": config, "roofline": roofline,
            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + (0 if (share_rgb and depth > 1) else frames[0]["live"]["rgba"].nbytes),
-                   "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps,
+                   "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps, "last_frame_abs_translation_error_m": pose_err_e2e,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
            "gpu_launches": (5 * args.steps + 1) if (share_rgb and depth > 1) else 6 * args.steps,  # per frame: k_populate x2 (x3 when the previous image is reloaded), k_maps_pyramid, k_icp_depth, k_track
            "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
