@@ -208,12 +208,15 @@ def main():
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 1024)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--wait", type=int, default=2, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep-then-poll")
+    ap.add_argument("--wait", type=int, default=-1, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep then poll + yield, 3 sleep then poll + 20 us sleeps; default: 2, or 3 when the ranks of this box have more tracker threads than host cores")
     ap.add_argument("--driver", default="native", choices=["native", "python"], help="who runs the trackers' host threads when they share the GPU: the library's sequence runner or Python threads")
     ap.add_argument("--no-share-rgb", action="store_true", help="pipelined trackers reload the previous frame's image instead of taking its pyramid from the tracker that has it")
     ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
     args = ap.parse_args()
 
+    if args.wait < 0:
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+        args.wait = 3 if local_world * max(1, args.pipeline) > len(os.sched_getaffinity(0)) else 2
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -46,7 +46,7 @@ struct dms_odom {
   cudaEvent_t ev_rgb;    // recorded after every initRGB: the intensity pyramid in rgb_pyr[] is complete (init_first_rgb_from waits on it)
   unsigned char* rgb_pyr[3];  // memory that received the image of the last initRGB (stable across the nextImage / lastNextImage pointer swap)
   cudaEvent_t ev_done;   // blocking-sync event (dms_odom_set_wait): the host thread sleeps instead of spinning
-  int blocking_wait;     // 0 spin, 1 blocking-sync event, 2 sleep for most of the expected wait, then poll and yield
+  int blocking_wait;     // 0 spin, 1 blocking-sync event, 2 sleep for most of the expected wait, then poll and yield, 3 same but poll with 20 us sleeps
   double wait_ema_us;    // running estimate of the wait (mode 2)
   std::string err;
 };
@@ -254,7 +254,7 @@ int dms_odom_set_block(dms_odom* h, int threads) {
   if (all || h->grid > g) h->grid = g;
   return DMS_OK;
 }
-int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 2) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
+int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 3) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
 int dms_odom_set_timing(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->timing = enabled ? 1 : 0; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 
@@ -424,10 +424,12 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
   if (!h || !trans || !rot) return fail(h, DMS_ERR_INVALID, "track_collect: null argument");
   Bind b(h->device);
   cudaError_t e;
-  if (h->blocking_wait == 2) {
+  if (h->blocking_wait >= 2) {
     const auto t0 = std::chrono::steady_clock::now();
     if (h->wait_ema_us > 150.0) std::this_thread::sleep_for(std::chrono::nanoseconds((long long)(h->wait_ema_us * 850.0)));
-    while ((e = cudaEventQuery(h->ev_done)) == cudaErrorNotReady) sched_yield();
+    while ((e = cudaEventQuery(h->ev_done)) == cudaErrorNotReady) {
+      if (h->blocking_wait == 3) std::this_thread::sleep_for(std::chrono::microseconds(20)); else sched_yield();
+    }
     const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
     h->wait_ema_us = h->wait_ema_us == 0.0 ? us : 0.8 * h->wait_ema_us + 0.2 * us;
   } else {

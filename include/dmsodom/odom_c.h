@@ -80,7 +80,8 @@ int dms_odom_set_grid(dms_odom* h, int n_ctas);
 int dms_odom_set_block(dms_odom* h, int threads);
 /* How dms_odom_track / dms_odom_track_collect wait for the result: 0 = spin on the stream (lowest latency, default),
  * 1 = sleep on a blocking-sync event, 2 = sleep for 85 % of the running average of the last waits, then poll and yield
- * (many trackers / ranks per host core without the wake-up latency of 1). */
+ * (many trackers / ranks per host core without the wake-up latency of 1), 3 = as 2 but polling with 20 us sleeps instead
+ * of yields (more waiting threads than host cores). */
 int dms_odom_set_wait(dms_odom* h, int mode);
 int dms_odom_set_timing(dms_odom* h, int enabled);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
