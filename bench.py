@@ -288,7 +288,7 @@ def main():
             per_sm = max(1, 1024 // threads) if threads else 1
             h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // min(depth, 8)))  # at most 8 kernels resident; further trackers queue and take the slots as they free up
             h.set_wait(args.wait if depth > 1 else 0)   # trackers sharing the GPU: do not burn a host core per tracker while waiting
-            h.set_timing(True)
+            h.set_timing(1)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss
 
@@ -442,7 +442,7 @@ def main():
         from densemonoslam_b200.sequence import SequenceTracker
         seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth, block_threads=args.threads,
                               grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
-                              fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0)
+                              fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
         config["driver"] = "dms_sequence_run (native host threads)"
         pipe = None
         ms, ktimes, iters_seen, so3_seen, clocks, last = timed_native(seq, args.steps, args.warmup, False)

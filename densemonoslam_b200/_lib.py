@@ -21,7 +21,7 @@ class DmsResult(C.Structure):
 class DmsTiming(C.Structure):
     _fields_ = [("track_ms", C.c_float), ("so3Step_ms", C.c_float), ("computeRgbResidual_ms", C.c_float),
                 ("icpStep_ms", C.c_float), ("rgbStep_ms", C.c_float), ("prologue_ms", C.c_float), ("serial_so3_ms", C.c_float),
-                ("serial_a_ms", C.c_float), ("serial_b_ms", C.c_float)]
+                ("serial_a_ms", C.c_float), ("serial_b_ms", C.c_float), ("barrier_wait_ms", C.c_float)]
 
 
 class DmsIterRecord(C.Structure):
@@ -69,7 +69,8 @@ class DmsSeqResult(C.Structure):
 
 class DmsSeqOptions(C.Structure):
     _fields_ = [("n_trackers", C.c_int), ("block_threads", C.c_int), ("grid", C.c_int), ("wait_mode", C.c_int), ("rgbOnly", C.c_int),
-                ("icpWeight", C.c_float), ("pyramid", C.c_int), ("fastOdom", C.c_int), ("so3", C.c_int), ("depthCutoff", C.c_float)]
+                ("icpWeight", C.c_float), ("pyramid", C.c_int), ("fastOdom", C.c_int), ("so3", C.c_int), ("depthCutoff", C.c_float),
+                ("timing", C.c_int)]
 
 
 # int (*dms_predict_fn)(void* user, const float pose[16], int kind, int tick, void* stream, dms_model_view* out)

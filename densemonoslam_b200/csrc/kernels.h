@@ -17,22 +17,29 @@ cudaError_t launch_depth_bilateral(const unsigned short* src, int sp, unsigned s
 cudaError_t launch_depth_metric(const unsigned short* src, int sp, float* dst, int dp, int rows, int cols, float maxD, cudaStream_t s);
 
 // ---- track.cu
-static const int ACC_STRIDE = 16;   // unsigned long long words between accumulator slots (128 B)
-static const int ACC_SLOTS = 192;
+static const int ACC_STRIDE = 16;   // unsigned long long words between accumulator slots (128 B: one L2 line per word)
+// Accumulators of the persistent tracking kernel: ACC_SETS rotating sets of SET_SLOTS slots, one set per
+// accumulate-and-solve phase (an SO(3) evaluation or a Gauss-Newton iteration).  Every CTA reads the totals of a
+// phase itself, so a set is cleared two phases later, when every CTA is known to have read it.
+static const int SET_SLOTS = 128;
+static const int ACC_SETS = 4;
+static const int STEP_SLOTS = 192;  // accumulator slots of the stand-alone step operators (behind the sets)
+static const int ACC_SLOTS = ACC_SETS * SET_SLOTS + STEP_SLOTS;
 static const int MAX_TRACE = 160;   // >= 3*50 interMap iterations
 
 // Device-resident control block of the persistent tracking kernel.
-static const int SYNC_WORDS = 32 * 19;  // barrier words: arrive counter + 16 release-flag copies + 2 work-list counters, one 128-byte line each
-static const int SYNC_LISTN = 32 * 17;  // sync[SYNC_LISTN + 32 * parity]: number of entries of the photometric segment list
-// Words of Ctrl::pub, the block the solver publishes for the workers' next phase (read once per CTA per barrier).
+static const int SYNC_WORDS = 32 * 4;   // barrier words, one 128-byte line each: [0] arrive counter (+ abort flag in word 1), [32],[64] work-list counters
+static const int SYNC_LISTN = 32 * 1;   // sync[SYNC_LISTN + 32 * parity]: number of entries of the photometric segment list
+// Words of the per-CTA block of constants the solver warp leaves in shared memory for the next phase.
 enum { PUB_RCURR = 0, PUB_TCURR = 9, PUB_KRKINV = 12, PUB_KT = 21, PUB_SIGMA = 24, PUB_BRK = 25, PUB_SO3DONE = 26,
        PUB_SO3H = 27, PUB_SO3KINV = 36, PUB_SO3KRLR = 45, PUB_WORDS = 64 };
 struct Ctrl {
-  float pub[PUB_WORDS];      // 256 bytes = two lines; ints are stored as bit patterns
-  unsigned int bad, pad0;
+  unsigned int aborted, pad0;   // 1: a grid barrier timed out (a CTA never arrived); the results are invalid
   int n_trace, n_dbg;
-  unsigned long long t_so3, t_phaseA, t_phaseB, t_mark;  // ns spent per phase kind (Stopwatch keys)
-  unsigned long long t_ser_so3, t_ser_a, t_ser_b, t_start, t_prologue;  // of which: inside the serial sections
+  // timing mode: ns per phase kind (Stopwatch keys) as seen by CTA 0; t_ser_*: of which in the serial section after the
+  // barrier (accumulator read-out, solve, pose update), t_wait: of which waiting at grid barriers
+  unsigned long long t_so3, t_phaseA, t_phaseB, t_mark;
+  unsigned long long t_ser_so3, t_ser_a, t_ser_b, t_start, t_prologue, t_wait;
   dms_odom_result res;
   float out_R[9], out_t[3];
 };
@@ -47,11 +54,11 @@ struct TrackParams {
   double Kd[3][9], Kinv[3][9];  // level intrinsics matrix and its inverse (RO.cpp:415-421, K.inverse())
   Ctrl* ctrl;
   unsigned int* sync;
-  unsigned long long* acc;
+  unsigned long long* acc;  // ACC_SETS sets, all zero between launches
   dms_iter_record* trace;
   int timing;
   unsigned int* seglist;    // segments with at least one photometric term in the current iteration (any order), lv[0] segments long
-  unsigned long long* dbg;  // timing mode: CTA 0 logs {tag, globaltimer} pairs here (MAX_DBG pairs)
+  unsigned long long* dbg;  // timeline mode: CTA 0 logs {tag, globaltimer} pairs here (MAX_DBG pairs)
 };
 static const int MAX_DBG = 1024;
 

@@ -25,7 +25,8 @@ struct dms_odom {
   float* zdepth;         // level-0 depth of the last loaded vertex map (stands in for vmaps_tmp, RO.cpp:104,213)
   Ctrl* ctrl;
   unsigned int* sync;
-  unsigned long long* acc;
+  unsigned long long* acc;       // ACC_SETS sets of the tracking kernel, then the step operators' block
+  unsigned long long* step_acc;  // = acc + ACC_SETS * SET_SLOTS * ACC_STRIDE
   dms_iter_record* trace;
   StepOut* step_out;
   unsigned long long* dbg;
@@ -46,6 +47,8 @@ struct dms_odom {
   cudaEvent_t ev_rgb;    // recorded after every initRGB: the intensity pyramid in rgb_pyr[] is complete (init_first_rgb_from waits on it)
   unsigned char* rgb_pyr[3];  // memory that received the image of the last initRGB (stable across the nextImage / lastNextImage pointer swap)
   cudaEvent_t ev_done;   // blocking-sync event (dms_odom_set_wait): the host thread sleeps instead of spinning
+  cudaStream_t track_stream;  // stream of the pending track_async
+  int in_flight;         // a track_async has not been collected yet
   int blocking_wait;     // 0 spin, 1 blocking-sync event, 2 sleep for most of the expected wait, then poll and yield, 3 same but poll with 20 us sleeps
   double wait_ema_us;    // running estimate of the wait (mode 2)
   std::string err;
@@ -136,6 +139,8 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   h->distThres = distThresh; h->angleThres = angleThresh;
   h->slab = nullptr; h->stage_v4 = h->stage_n4 = nullptr; h->stage_rgba = nullptr; h->stage_depth = nullptr;
   h->h_ctrl = nullptr; h->h_step = nullptr; h->timing = 0; h->tracing = 0; h->ev0 = h->ev1 = nullptr;
+  h->in_flight = 0; h->track_stream = nullptr; h->blocking_wait = 0; h->wait_ema_us = 0.0; h->wait_reader = nullptr;
+  h->ev_rgb = h->ev_took = h->ev_done = nullptr; h->rgb_pyr[0] = h->rgb_pyr[1] = h->rgb_pyr[2] = nullptr;
   memset(&h->last, 0, sizeof h->last); memset(&h->last_timing, 0, sizeof h->last_timing);
   // RO.cpp:26-31 initial public state
   h->last.lastICPCount = h->last.lastRGBCount = h->last.lastSO3Count = (float)(width * height);
@@ -186,6 +191,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   e = cudaMemset(h->slab, 0, h->slab_bytes);  // the reference leaves buffers uninitialised
   off = 0;
   for (int r = 0; r < nreq; ++r) { *reqs[r].p = h->slab + off; off += align_up(reqs[r].bytes, 256); }
+  h->step_acc = h->acc + (size_t)ACC_SETS * SET_SLOTS * ACC_STRIDE;
   if (e == cudaSuccess) e = cudaMallocHost(&h->h_ctrl, sizeof(Ctrl));
   if (e == cudaSuccess) e = cudaMallocHost(&h->h_step, sizeof(StepOut));
   if (e == cudaSuccess) {
@@ -255,7 +261,7 @@ int dms_odom_set_block(dms_odom* h, int threads) {
   return DMS_OK;
 }
 int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 3) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
-int dms_odom_set_timing(dms_odom* h, int enabled) { if (!h) return DMS_ERR_INVALID; h->timing = enabled ? 1 : 0; return DMS_OK; }
+int dms_odom_set_timing(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 2) return DMS_ERR_INVALID; h->timing = mode; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 
 // ------------------------------------------------------------------ pyramid construction
@@ -384,6 +390,7 @@ int dms_odom_init_first_rgb_host(dms_odom* h, const uint8_t* src, size_t pitch, 
 int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], int rgbOnly, float icpWeight, int pyramid, int fastOdom,
                          int so3, int interMap, void* stream) {
   if (!h || !trans || !rot) return fail(h, DMS_ERR_INVALID, "track: null argument");
+  if (h->in_flight) return fail(h, DMS_ERR_INVALID, "track_async: the previous track has not been collected");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
   TrackParams P;
@@ -407,14 +414,16 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
     memcpy(P.Kd[i], Kd, sizeof Kd); memcpy(P.Kinv[i], Ki, sizeof Ki);
   }
   P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = h->timing;
-  P.dbg = h->timing ? h->dbg : nullptr;
+  P.dbg = h->timing >= 2 ? h->dbg : nullptr;  // the timeline probes run only on request (set_timing(h, 2))
   P.seglist = h->seglist;
-  if (h->timing) { CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s)); CK(cudaEventRecord(h->ev0, s)); }
+  if (h->timing >= 2) CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s));
+  if (h->timing) CK(cudaEventRecord(h->ev0, s));
   cudaError_t e = launch_track(P, h->grid, h->tpb, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
   if (h->timing) CK(cudaEventRecord(h->ev1, s));
   CK(cudaMemcpyAsync(h->h_ctrl, h->ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
-  if (h->blocking_wait) CK(cudaEventRecord(h->ev_done, s));
+  CK(cudaEventRecord(h->ev_done, s));  // collect waits on this event, whatever stream it is given
+  h->in_flight = 1; h->track_stream = s;
   if (so3)  // RO.cpp:595-601: the kernel holds the old pointers, so the swap can be applied right away
     for (int i = 0; i < 3; ++i) { unsigned char* t = h->lv[i].lastNextImage; h->lv[i].lastNextImage = h->lv[i].nextImage; h->lv[i].nextImage = t; }
   return DMS_OK;
@@ -424,6 +433,9 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
   if (!h || !trans || !rot) return fail(h, DMS_ERR_INVALID, "track_collect: null argument");
   Bind b(h->device);
   cudaError_t e;
+  (void)stream;  // the result is ordered by the event recorded on the stream the track was launched on
+  if (!h->in_flight) return fail(h, DMS_ERR_INVALID, "track_collect: no track pending");
+  h->in_flight = 0;
   if (h->blocking_wait >= 2) {
     const auto t0 = std::chrono::steady_clock::now();
     if (h->wait_ema_us > 150.0) std::this_thread::sleep_for(std::chrono::nanoseconds((long long)(h->wait_ema_us * 850.0)));
@@ -432,16 +444,21 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
     }
     const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
     h->wait_ema_us = h->wait_ema_us == 0.0 ? us : 0.8 * h->wait_ema_us + 0.2 * us;
+  } else if (h->blocking_wait == 1) {
+    e = cudaEventSynchronize(h->ev_done);
   } else {
-    e = h->blocking_wait ? cudaEventSynchronize(h->ev_done) : cudaStreamSynchronize((cudaStream_t)stream);
+    while ((e = cudaEventQuery(h->ev_done)) == cudaErrorNotReady) { }  // spin: lowest latency
   }
-  if (e != cudaSuccess) {
-    // a failed launch leaves the barrier words undefined: rearm them
+  const bool aborted = e == cudaSuccess && h->h_ctrl->aborted != 0u;
+  if (e != cudaSuccess || aborted) {
+    // a failed launch or an aborted grid barrier leaves the barrier words and accumulators undefined: rearm them
+    cudaStreamSynchronize(h->track_stream);
     memset(h->h_ctrl, 0, sizeof(Ctrl));
     h->h_ctrl->res = h->last;
     cudaMemcpy(h->ctrl, h->h_ctrl, sizeof(Ctrl), cudaMemcpyHostToDevice);
     cudaMemset(h->acc, 0, (size_t)ACC_SLOTS * ACC_STRIDE * sizeof(unsigned long long));
     cudaMemset(h->sync, 0, sizeof(unsigned int) * SYNC_WORDS);
+    if (aborted) return fail(h, DMS_ERR_DEVICE, "k_track: a grid barrier timed out (a thread block never arrived)");
     return fail(h, (int)e, "k_track");
   }
   const Ctrl* C = h->h_ctrl;
@@ -459,6 +476,7 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
     h->last_timing.serial_so3_ms = (float)(C->t_ser_so3 * 1e-6);
     h->last_timing.serial_a_ms = (float)(C->t_ser_a * 1e-6);
     h->last_timing.serial_b_ms = (float)(C->t_ser_b * 1e-6);
+    h->last_timing.barrier_wait_ms = (float)(C->t_wait * 1e-6);
   }
   return DMS_OK;
 }
@@ -524,7 +542,7 @@ int dms_odom_icp_step(dms_odom* h, int level, const float Rcurr[9], const float 
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
   const Level& L = h->lv[level];
-  CK(launch_icp_step(L, Rcurr, tcurr, Rprev_inv, tprev, h->distThres, h->angleThres, h->acc, h->step_out, h_mask ? h->mask : nullptr,
+  CK(launch_icp_step(L, Rcurr, tcurr, Rprev_inv, tprev, h->distThres, h->angleThres, h->step_acc, h->step_out, h_mask ? h->mask : nullptr,
                      h->lv[0].pitch_u8, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out28) memcpy(out28, h->h_step->vals, sizeof(float) * 28);
@@ -537,7 +555,7 @@ int dms_odom_rgb_residual(dms_odom* h, int level, const float kt[3], const float
   if (!h || level < 0 || level > 2 || !kt || !krkinv) return fail(h, DMS_ERR_INVALID, "rgb_residual: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_rgb_residual(h->lv[level], kt, krkinv, h->acc, h->step_out, s));
+  CK(launch_rgb_residual(h->lv[level], kt, krkinv, h->step_acc, h->step_out, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (count) *count = h->h_step->count;
   if (sigma) *sigma = h->h_step->sigma;
@@ -548,7 +566,7 @@ int dms_odom_rgb_step(dms_odom* h, int level, float sigma, float out28[28], int6
   if (!h || level < 0 || level > 2) return fail(h, DMS_ERR_INVALID, "rgb_step: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_rgb_step(h->lv[level], sigma, h->acc, h->step_out, s));
+  CK(launch_rgb_step(h->lv[level], sigma, h->step_acc, h->step_out, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out28) memcpy(out28, h->h_step->vals, sizeof(float) * 28);
   if (count) *count = h->h_step->count;
@@ -560,7 +578,7 @@ int dms_odom_so3_step(dms_odom* h, int level, const float H[9], const float kinv
   if (!h || level < 0 || level > 2 || !H || !kinv || !krlr) return fail(h, DMS_ERR_INVALID, "so3_step: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_so3_step(h->lv[level], H, kinv, krlr, h->acc, h->step_out, s));
+  CK(launch_so3_step(h->lv[level], H, kinv, krlr, h->step_acc, h->step_out, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out10) memcpy(out10, h->h_step->vals, sizeof(float) * 10);
   if (count) *count = h->h_step->count;

@@ -24,6 +24,9 @@ struct Flags {  // monotone per-frame flags, waited on by other threads
 
 }  // namespace
 
+// One run of the sequence, as seen by the worker threads.
+struct Job { const dms_seq_frame* frames; int n; const uint8_t* first_prev; int host; dms_seq_result* out; };
+
 struct dms_sequence {
   int device, width, height;
   dms_seq_options opt;
@@ -31,73 +34,41 @@ struct dms_sequence {
   std::vector<cudaStream_t> streams;
   int grid, resident;
   Flags issued, taken;
+  // worker pool: one host thread per tracker, created once and parked between runs (spawning them per run cost a
+  // fixed ~2 ms per call, which dominated short runs and multi-rank launches)
+  std::vector<std::thread> workers;
+  std::mutex m; std::condition_variable cv_go, cv_done;
+  unsigned long long run_id = 0; int pending = 0; bool quit = false;
+  Job job{}; std::atomic<int> err{0};
 };
 
-extern "C" {
-
-void dms_sequence_default_options(dms_seq_options* o) {
-  if (!o) return;
-  o->n_trackers = 12; o->block_threads = 512; o->grid = 0; o->wait_mode = 2;
-  o->rgbOnly = 0; o->icpWeight = 10.0f; o->pyramid = 1; o->fastOdom = 0; o->so3 = 1; o->depthCutoff = 25.0f;
-}
-
-int dms_sequence_destroy(dms_sequence* s) {
-  if (!s) return DMS_OK;
+static void seq_work(dms_sequence* s, int k);
+static void seq_worker_main(dms_sequence* s, int k) {
   cudaSetDevice(s->device);
-  for (size_t i = 0; i < s->trk.size(); ++i) if (s->trk[i]) dms_odom_destroy(s->trk[i]);
-  for (size_t i = 0; i < s->streams.size(); ++i) if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
-  delete s;
-  return DMS_OK;
-}
-
-int dms_sequence_create(dms_sequence** out, int device, int width, int height, float cx, float cy, float fx, float fy, const dms_seq_options* opt) {
-  if (!out) return DMS_ERR_INVALID;
-  *out = nullptr;
-  dms_seq_options o;
-  if (opt) o = *opt; else dms_sequence_default_options(&o);
-  if (o.n_trackers < 1 || o.n_trackers > 64) return DMS_ERR_INVALID;
-  dms_sequence* s = new (std::nothrow) dms_sequence();
-  if (!s) return DMS_ERR_NOMEM;
-  s->device = device; s->width = width; s->height = height; s->opt = o; s->grid = 0; s->resident = 1;
-  cudaSetDevice(device);
-  int sms = 0;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-  const float angle = sinf(20.f * 3.14159254f / 180.f);
-  for (int k = 0; k < o.n_trackers; ++k) {
-    dms_odom* h = nullptr;
-    int rc = dms_odom_create(&h, device, width, height, cx, cy, fx, fy, 0.10f, angle);
-    if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; }
-    s->trk.push_back(h);
-    cudaStream_t st = nullptr;
-    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { dms_sequence_destroy(s); return DMS_ERR_DEVICE; }
-    s->streams.push_back(st);
-    if (o.n_trackers > 1) {
-      const int threads = o.block_threads > 0 ? o.block_threads : 1024;
-      if (o.block_threads > 0) { rc = dms_odom_set_block(h, o.block_threads); if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; } }
-      const int slots = sms * (1024 / threads > 0 ? 1024 / threads : 1);
-      s->grid = o.grid > 0 ? o.grid : slots / (o.n_trackers < 8 ? o.n_trackers : 8);
-      dms_odom_set_grid(h, s->grid);
-      s->resident = slots / s->grid < o.n_trackers ? slots / s->grid : o.n_trackers;
-      dms_odom_set_wait(h, o.wait_mode);
+  unsigned long long seen = 0;
+  for (;;) {
+    {
+      std::unique_lock<std::mutex> l(s->m);
+      s->cv_go.wait(l, [&] { return s->quit || s->run_id != seen; });
+      if (s->quit) return;
+      seen = s->run_id;
     }
-    dms_odom_set_timing(h, 1);
+    seq_work(s, k);
+    {
+      std::lock_guard<std::mutex> l(s->m);
+      if (--s->pending == 0) s->cv_done.notify_all();
+    }
   }
-  *out = s;
-  return DMS_OK;
 }
 
-int dms_sequence_resident(const dms_sequence* s) { return s ? s->resident : 0; }
-
-int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const uint8_t* first_prev, int host, dms_seq_result* out) {
-  if (!s || !frames || !out || n < 0 || (n > 0 && !first_prev)) return DMS_ERR_INVALID;
+// Frames k, k + K, k + 2K, ... of the running job on tracker k.
+static void seq_work(dms_sequence* s, int k) {
   const int K = (int)s->trk.size();
   const dms_seq_options& o = s->opt;
-  s->issued.reset((size_t)n + 1);
-  s->taken.reset((size_t)n + K + 1);
-  for (int j = 0; j < K; ++j) s->taken.set((size_t)j);
-  std::atomic<int> err(0);
-  auto work = [&](int k) {
-    cudaSetDevice(s->device);
+  const dms_seq_frame* frames = s->job.frames; const int n = s->job.n; const uint8_t* first_prev = s->job.first_prev;
+  const int host = s->job.host; dms_seq_result* out = s->job.out;
+  std::atomic<int>& err = s->err;
+  {
     dms_odom* h = s->trk[k];
     void* st = (void*)s->streams[k];
     for (int i = k; i < n && !err.load(); i += K) {
@@ -138,15 +109,88 @@ int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const 
       dms_odom_get_timing(h, &tm);
       out[i].track_ms = tm.track_ms;
     }
-  };
-  if (K == 1) {
-    work(0);
-  } else {
-    std::vector<std::thread> th;
-    for (int k = 0; k < K; ++k) th.emplace_back(work, k);
-    for (auto& t : th) t.join();
   }
-  return err.load();
+}
+
+extern "C" {
+
+void dms_sequence_default_options(dms_seq_options* o) {
+  if (!o) return;
+  o->n_trackers = 12; o->block_threads = 512; o->grid = 0; o->wait_mode = 2;
+  o->rgbOnly = 0; o->icpWeight = 10.0f; o->pyramid = 1; o->fastOdom = 0; o->so3 = 1; o->depthCutoff = 25.0f;
+  o->timing = 0;
+}
+
+int dms_sequence_destroy(dms_sequence* s) {
+  if (!s) return DMS_OK;
+  { std::lock_guard<std::mutex> l(s->m); s->quit = true; }
+  s->cv_go.notify_all();
+  for (auto& t : s->workers) if (t.joinable()) t.join();
+  cudaSetDevice(s->device);
+  for (size_t i = 0; i < s->trk.size(); ++i) if (s->trk[i]) dms_odom_destroy(s->trk[i]);
+  for (size_t i = 0; i < s->streams.size(); ++i) if (s->streams[i]) cudaStreamDestroy(s->streams[i]);
+  delete s;
+  return DMS_OK;
+}
+
+int dms_sequence_create(dms_sequence** out, int device, int width, int height, float cx, float cy, float fx, float fy, const dms_seq_options* opt) {
+  if (!out) return DMS_ERR_INVALID;
+  *out = nullptr;
+  dms_seq_options o;
+  if (opt) o = *opt; else dms_sequence_default_options(&o);
+  if (o.n_trackers < 1 || o.n_trackers > 64) return DMS_ERR_INVALID;
+  dms_sequence* s = new (std::nothrow) dms_sequence();
+  if (!s) return DMS_ERR_NOMEM;
+  s->device = device; s->width = width; s->height = height; s->opt = o; s->grid = 0; s->resident = 1;
+  cudaSetDevice(device);
+  int sms = 0;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const float angle = sinf(20.f * 3.14159254f / 180.f);
+  for (int k = 0; k < o.n_trackers; ++k) {
+    dms_odom* h = nullptr;
+    int rc = dms_odom_create(&h, device, width, height, cx, cy, fx, fy, 0.10f, angle);
+    if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; }
+    s->trk.push_back(h);
+    cudaStream_t st = nullptr;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { dms_sequence_destroy(s); return DMS_ERR_DEVICE; }
+    s->streams.push_back(st);
+    if (o.n_trackers > 1) {
+      const int threads = o.block_threads > 0 ? o.block_threads : 1024;
+      if (o.block_threads > 0) { rc = dms_odom_set_block(h, o.block_threads); if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; } }
+      const int slots = sms * (1024 / threads > 0 ? 1024 / threads : 1);
+      s->grid = o.grid > 0 ? o.grid : slots / (o.n_trackers < 8 ? o.n_trackers : 8);
+      dms_odom_set_grid(h, s->grid);
+      s->resident = slots / s->grid < o.n_trackers ? slots / s->grid : o.n_trackers;
+      dms_odom_set_wait(h, o.wait_mode);
+    }
+    dms_odom_set_timing(h, o.timing);
+  }
+  if (o.n_trackers > 1)
+    for (int k = 0; k < o.n_trackers; ++k) s->workers.emplace_back(seq_worker_main, s, k);
+  *out = s;
+  return DMS_OK;
+}
+
+int dms_sequence_resident(const dms_sequence* s) { return s ? s->resident : 0; }
+
+int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const uint8_t* first_prev, int host, dms_seq_result* out) {
+  if (!s || !frames || !out || n < 0 || (n > 0 && !first_prev)) return DMS_ERR_INVALID;
+  const int K = (int)s->trk.size();
+  s->issued.reset((size_t)n + 1);
+  s->taken.reset((size_t)n + K + 1);
+  for (int j = 0; j < K; ++j) s->taken.set((size_t)j);
+  s->err.store(0);
+  s->job.frames = frames; s->job.n = n; s->job.first_prev = first_prev; s->job.host = host; s->job.out = out;
+  if (K == 1) {
+    cudaSetDevice(s->device);
+    seq_work(s, 0);
+  } else {
+    std::unique_lock<std::mutex> l(s->m);
+    s->pending = K; ++s->run_id;
+    s->cv_go.notify_all();
+    s->cv_done.wait(l, [&] { return s->pending == 0; });
+  }
+  return s->err.load();
 }
 
 }  // extern "C"

@@ -248,8 +248,9 @@ class RGBDOdometry:
         """0 spin (default), 1 blocking-sync event, 2 sleep for most of the expected wait then poll and yield."""
         self._ck(self._L.dms_odom_set_wait(self._h, int(mode)), "set_wait")
 
-    def set_timing(self, enabled=True):
-        self._ck(self._L.dms_odom_set_timing(self._h, int(enabled)), "set_timing")
+    def set_timing(self, mode=1):
+        """0 = off, 1 = kernel events + per-phase counters, 2 = additionally the timeline of timeline()."""
+        self._ck(self._L.dms_odom_set_timing(self._h, int(mode)), "set_timing")
 
     def timing(self):
         t = _lib.DmsTiming()
@@ -257,7 +258,7 @@ class RGBDOdometry:
         # the reference's Stopwatch keys (RO.cpp:336,444,495,525)
         return {"track": t.track_ms, "so3Step": t.so3Step_ms, "computeRgbResidual": t.computeRgbResidual_ms,
                 "icpStep": t.icpStep_ms, "rgbStep": t.rgbStep_ms, "prologue": t.prologue_ms, "serial_so3": t.serial_so3_ms,
-                "serial_a": t.serial_a_ms, "serial_b": t.serial_b_ms}
+                "serial_a": t.serial_a_ms, "serial_b": t.serial_b_ms, "barrier_wait": t.barrier_wait_ms}
 
     # ------------------------------------------------------------------ step operators (cudafuncs.cuh free functions)
     def icpStep(self, level, Rcurr, tcurr, Rprev_inv, tprev, want_mask=False, stream=None):

@@ -57,9 +57,10 @@ typedef struct dms_odom_result {
 typedef struct dms_odom_timing {
   float track_ms;   /* whole getIncrementalTransformation on the device */
   float so3Step_ms, computeRgbResidual_ms, icpStep_ms, rgbStep_ms; /* split by the kernel's own phase timers */
-  /* diagnostics: derivative prologue, and the part of each key spent in the single-CTA serial sections
-   * (accumulator read-out, solve, pose update) while the rest of the grid waits */
+  /* diagnostics: derivative prologue, and the part of each key spent in the serial section after a grid barrier
+   * (accumulator read-out, solve, pose update: run by one warp of every thread block, the others wait) */
   float prologue_ms, serial_so3_ms, serial_a_ms, serial_b_ms;
+  float barrier_wait_ms; /* of the keys above: thread block 0 waiting at grid barriers (includes load imbalance) */
 } dms_odom_timing;
 
 /* ---- lifetime: RGBDOdometry::RGBDOdometry / ~RGBDOdometry (RO.cpp:21-116).
@@ -83,7 +84,9 @@ int dms_odom_set_block(dms_odom* h, int threads);
  * (many trackers / ranks per host core without the wake-up latency of 1), 3 = as 2 but polling with 20 us sleeps instead
  * of yields (more waiting threads than host cores). */
 int dms_odom_set_wait(dms_odom* h, int mode);
-int dms_odom_set_timing(dms_odom* h, int enabled);
+/* mode 0 = off (default), 1 = CUDA events around the kernel + per-phase counters of thread block 0 (a few clock reads per
+ * phase), 2 = additionally the {tag, timestamp} timeline read by dms_odom_get_timeline (a memset per track). */
+int dms_odom_set_timing(dms_odom* h, int mode);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
 
 /* ---- pyramid construction.
@@ -169,7 +172,7 @@ typedef struct dms_iter_record {
 } dms_iter_record;
 int dms_odom_set_trace(dms_odom* h, int enabled); /* off by default: recording costs a little solver time */
 int dms_odom_get_trace(dms_odom* h, dms_iter_record* h_records, int max_records, int* n_records);
-/* Timing mode only: {tag, nanosecond timestamp} pairs logged by CTA 0 of the tracking kernel at its phase
+/* Timing mode 2 only: {tag, nanosecond timestamp} pairs logged by CTA 0 of the tracking kernel at its phase
  * boundaries during the last track call (diagnostic for tools/track_timing.py). */
 int dms_odom_get_timeline(dms_odom* h, uint64_t* h_pairs, int max_pairs, int* n_pairs);
 

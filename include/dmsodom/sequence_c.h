@@ -28,7 +28,7 @@ typedef struct dms_seq_frame {
 typedef struct dms_seq_result {
   float pose[16];             /* refined pose, row-major */
   dms_odom_result r;
-  float track_ms;             /* device time of the tracking kernel of this frame */
+  float track_ms;             /* device time of the tracking kernel of this frame (options.timing != 0) */
 } dms_seq_result;
 
 typedef struct dms_seq_options {
@@ -38,6 +38,7 @@ typedef struct dms_seq_options {
   int wait_mode;              /* dms_odom_set_wait */
   int rgbOnly; float icpWeight; int pyramid, fastOdom, so3;
   float depthCutoff;
+  int timing;                 /* dms_odom_set_timing of every tracker (0 = off: track_ms of the results stays 0) */
 } dms_seq_options;
 void dms_sequence_default_options(dms_seq_options* o);
 

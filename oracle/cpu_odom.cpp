@@ -646,7 +646,6 @@ static inline double rcp_nr(double d) {
   r = fma(r, fma(-d, r, 1.0), r);
   return r;
 }
-static inline float rcp_nr(float d) { return 1.0f / d; }  // the 3x3 fp32 system keeps IEEE division
 
 // sin / cos for Rodrigues.  Below 0.25 rad (every realistic Gauss-Newton update) an explicit Taylor
 // polynomial in plain fp64 mul/add: truncation < 2e-25, and bit-identical on CPU and GPU.  Larger angles
@@ -678,8 +677,14 @@ static inline void sincos_small(double t, double* sn, double* cs) {
   }
 }
 
-// LDL^T solve without pivoting (stands in for Eigen ldlt().solve, RO.cpp:554-566,371).
-// One reciprocal per pivot, then multiplications (the device solver does the same).
+// Reciprocal of an LDL^T pivot.  Eigen's LDLT::solve (RO.cpp:554-566,371) sets the components whose |D| is not above
+// its tolerance to zero instead of dividing, so a vanishing pivot (no correspondences: A = 0, b = 0) gives a zero step
+// and the prior pose, not NaN.  The threshold is the smallest normal fp32 (the fp32 seed of rcp_nr must be finite).
+static inline double pivot_rcp(double d) { const double r = rcp_nr(d); return std::fabs(d) > 1.17549435e-38 ? r : 0.0; }
+static inline float pivot_rcp(float d) { return std::fabs(d) > 1.17549435e-38f ? 1.0f / d : 0.0f; }
+
+// LDL^T solve without pivoting (stands in for Eigen ldlt().solve, RO.cpp:371) of the 3x3 fp32 SO(3) system.
+// One reciprocal per pivot, then multiplications (the device evaluates the same sequence in every lane).
 template <class T, int N>
 static void ldlt_solve(const T* A, const T* b, T* x) {
   T L[N * N], D[N], iD[N], y[N];
@@ -688,7 +693,7 @@ static void ldlt_solve(const T* A, const T* b, T* x) {
     T d = A[j * N + j];
     for (int k = 0; k < j; ++k) d = d - (L[j * N + k] * L[j * N + k]) * D[k];
     D[j] = d;
-    iD[j] = rcp_nr(d);
+    iD[j] = pivot_rcp(d);
     for (int i = j + 1; i < N; ++i) {
       T s = A[i * N + j];
       for (int k = 0; k < j; ++k) s = s - (L[i * N + k] * L[j * N + k]) * D[k];
@@ -705,6 +710,29 @@ static void ldlt_solve(const T* A, const T* b, T* x) {
     T s = y[i];
     for (int k = N - 1; k > i; --k) s = s - L[k * N + i] * x[k];  // last unknown first (right-looking order)
     x[i] = s;
+  }
+}
+
+// LDL^T solve of the 6x6 fp64 system (stands in for Eigen ldlt().solve, RO.cpp:554-566) in the form the device's
+// solver warp uses: right-looking on the lower triangle of the augmented matrix [A; b^T].  At pivot k every entry to
+// the right of column k takes s_rc -= (s_rk * s_ck) / D_k with the unscaled column k, then column k becomes
+// L_rk = s_rk / D_k.  Row N carries the right-hand side through the same updates (= forward substitution) and ends as
+// y = D^-1 L^-1 b; back substitution takes the last unknown first.
+template <int N>
+static void ldlt_solve_aug(const double* A, const double* b, double* x) {
+  double s[N + 1][N];
+  for (int r = 0; r < N; ++r) for (int c = 0; c <= r; ++c) s[r][c] = A[r * N + c];
+  for (int c = 0; c < N; ++c) s[N][c] = b[c];
+  for (int k = 0; k < N; ++k) {
+    const double iDk = pivot_rcp(s[k][k]);
+    for (int r = k + 1; r <= N; ++r)
+      for (int c = k + 1; c <= (r < N ? r : N - 1); ++c) s[r][c] = s[r][c] - (s[r][k] * s[c][k]) * iDk;
+    for (int r = k + 1; r <= N; ++r) s[r][k] = s[r][k] * iDk;
+  }
+  for (int i = N - 1; i >= 0; --i) {
+    double v = s[N][i];
+    for (int k = N - 1; k > i; --k) v = v - s[k][i] * x[k];
+    x[i] = v;
   }
 }
 
@@ -988,7 +1016,7 @@ struct Odom {
           for (int q = 0; q < 36; ++q) lastA[q] = A_rgb[q];
           for (int q = 0; q < 6; ++q) lastb[q] = b_rgb[q];
         }
-        ldlt_solve<double, 6>(lastA, lastb, result);
+        ldlt_solve_aug<6>(lastA, lastb, result);
         // OP.h:73-93 computeUpdateSE3
         double Ru[9]; rodrigues(result + 3, Ru);
         double U[16] = {Ru[0], Ru[1], Ru[2], result[0], Ru[3], Ru[4], Ru[5], result[1], Ru[6], Ru[7], Ru[8], result[2], 0, 0, 0, 1};

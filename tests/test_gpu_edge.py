@@ -32,20 +32,24 @@ def test_ragged_sizes(torch_cuda, orc, synth, wh):
     compare_track(g, o, pose[:3, 3].copy(), pose[:3, :3].copy(), FLAG_ROWS["frameToModel"])
 
 
-def test_empty_inputs_give_the_same_nans(torch_cuda, orc, synth, pair_small):
-    """No depth, empty model: zero correspondences everywhere; the degenerate solve propagates NaN exactly as in the oracle."""
+def test_empty_inputs_return_the_prior_pose(torch_cuda, orc, synth, pair_small):
+    """No depth, empty model: zero correspondences everywhere, A = 0 and b = 0.  Eigen's ldlt().solve (RO.cpp:554-566)
+    zeroes the components of vanishing pivots, so the step is zero and the prior pose comes back (not NaN); the error
+    fields are 0/0 = NaN as in the reference."""
     cam, model, live, T = pair_small
     g, o = both(orc, synth, cam)
     m = {k: np.zeros_like(v) for k, v in model.items()}
     l = {k: np.zeros_like(v) for k, v in live.items()}
-    pose = np.eye(4, dtype=np.float32)
+    pose = synth.pose_from((0.1, -0.2, 0.05), (0.3, 0.1, -0.2)).astype(np.float32)
     load_frame_to_model(torch_cuda, g, o, m, l, pose)
     check_pyramids(g, o)
     tg, Rg = g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["modelToModel"])
     to_, Ro, res = o.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["modelToModel"])
     assert g.lastICPCount == res.lastICPCount == 0 and g.lastRGBCount == res.lastRGBCount == 0
-    assert np.array_equal(tg, to_, equal_nan=True) and np.array_equal(Rg, Ro, equal_nan=True)
-    assert np.array_equal(np.isnan(g.lastA), np.isnan(np.array(res.A[:]).reshape(6, 6)))
+    assert np.array_equal(tg, to_) and np.array_equal(Rg, Ro)
+    assert np.all(np.isfinite(tg)) and np.all(np.isfinite(Rg))
+    assert np.max(np.abs(tg - pose[:3, 3])) <= 1e-6 and np.max(np.abs(Rg - pose[:3, :3])) <= 1e-6
+    assert np.array_equal(g.lastA, np.zeros((6, 6))) and np.array_equal(np.array(res.A[:]), np.zeros(36))
 
 
 def test_pitched_device_inputs(torch_cuda, orc, synth, pair_small):

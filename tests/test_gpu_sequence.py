@@ -25,7 +25,7 @@ def test_sequence_runner_equals_sequential_tracker(n_trackers, host):
     put = (lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()) if host else dev
     fl = [{"v": put(f["model"]["vmap4"]), "n": put(f["model"]["nmap4"]), "mi": put(f["model"]["rgba"]), "d": put(f["live"]["depth"]),
            "li": put(f["live"]["rgba"]), "prior": f["prior"]} for f in frames]
-    seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, n_trackers=n_trackers, block_threads=512, grid=20, wait_mode=2)
+    seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, n_trackers=n_trackers, block_threads=512, grid=20, wait_mode=2, timing=1)
     res = seq.run(seq.make_frames(fl), put(first_prev), host)
     assert seq.resident == min(n_trackers, 296 // 20) or n_trackers == 1
 

@@ -12,7 +12,7 @@ cam = {"vga": synth.CAM_VGA, "kitti": synth.CAM_KITTI, "1080p": synth.CAM_1080P,
 model, live, T = synth.frame_pair(cam, seed=1234)
 dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
 g = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
-g.set_timing(True)
+g.set_timing(int(os.environ.get('TL_MODE', '2')))
 pose = np.eye(4, dtype=np.float32)
 mv, mn, mi, ld, li = dev(model["vmap4"]), dev(model["nmap4"]), dev(model["rgba"]), dev(live["depth"]), dev(live["rgba"])
 g.initFirstRGB(mi)
@@ -36,8 +36,8 @@ for (a, ta), (b, tb) in zip(stl[:-1], stl[1:]):
 for k, (n, tot) in sagg.items():
     print(f"  {k:30s} n={n:3d} mean={tot / n:6.2f} us")
 t0 = tl[0][1]
-names = {10: "so3 start", 11: "so3 loop done (warp0)", 12: "so3 arrived", 13: "so3 barrier exit", 20: "A start L0", 21: "A start L1", 22: "A start L2",
-         30: "A loop done (warp0)", 31: "A arrived", 32: "A barrier exit", 40: "B loop done (warp0)", 41: "B arrived", 42: "B barrier exit", 99: "end"}
+names = {10: "so3 start", 11: "so3 flushed", 12: "so3 barrier passed", 13: "so3 solved", 20: "A start L0", 21: "A start L1", 22: "A start L2",
+         30: "A flushed", 31: "A barrier passed", 32: "A serial done", 40: "B flushed", 41: "B barrier passed", 43: "B scratch solve done", 42: "B solved", 99: "end"}
 prev = t0
 agg = {}
 last_tag = None
