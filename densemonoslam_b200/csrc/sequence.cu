@@ -154,14 +154,16 @@ int dms_sequence_create(dms_sequence** out, int device, int width, int height, f
     cudaStream_t st = nullptr;
     if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { dms_sequence_destroy(s); return DMS_ERR_DEVICE; }
     s->streams.push_back(st);
+    if (o.block_threads > 0) { rc = dms_odom_set_block(h, o.block_threads); if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; } }
     if (o.n_trackers > 1) {
       const int threads = o.block_threads > 0 ? o.block_threads : 1024;
-      if (o.block_threads > 0) { rc = dms_odom_set_block(h, o.block_threads); if (rc != DMS_OK) { dms_sequence_destroy(s); return rc; } }
       const int slots = sms * (1024 / threads > 0 ? 1024 / threads : 1);
       s->grid = o.grid > 0 ? o.grid : slots / (o.n_trackers < 8 ? o.n_trackers : 8);
       dms_odom_set_grid(h, s->grid);
       s->resident = slots / s->grid < o.n_trackers ? slots / s->grid : o.n_trackers;
       dms_odom_set_wait(h, o.wait_mode);
+    } else if (o.grid > 0) {
+      dms_odom_set_grid(h, o.grid);
     }
     dms_odom_set_timing(h, o.timing);
   }
