@@ -34,9 +34,15 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLAGS = dict(rgbOnly=False, icpWeight=10.0, pyramid=True, fastOdom=False, so3=True)
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch at 1241x376 (ncu --set full, profiles/): the working
-# set is L2-resident, so DRAM traffic is far BELOW the algorithmic bytes
-TRAFFIC_NCU = 32.9e6  # dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch of this command (profiles/r01_ncu_k_track_kitti.json)
+
+
+def traffic_of(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_track launch of this workload, from the committed ncu summary
+    (profiles/r02_traffic.json, written by tools/ncu_summary.py from an `ncu --set full` capture); None without a capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))[workload]["k_track_dram_bytes"]
+    except Exception:
+        return None
 
 
 def workload_def(name):
@@ -204,8 +210,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=12, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
-    ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 1024)")
+    ap.add_argument("--pipeline", type=int, default=8, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 768)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wait", type=int, default=-1, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep then poll + yield, 3 sleep then poll + 20 us sleeps; default: 2, or 3 when the ranks of this box have more tracker threads than host cores")
@@ -226,6 +232,7 @@ def main():
     iters_nominal = [3 if FLAGS["fastOdom"] else 10, 5 if FLAGS["pyramid"] else 0, 4 if FLAGS["pyramid"] else 0]
     config = {"workload": wl_desc, "width": cam.width, "height": cam.height, "icpWeight": FLAGS["icpWeight"], "iterations": iters_nominal,
               "so3": FLAGS["so3"], "parallelism": f"{world} independent sensor tracker(s), one per GPU, no collective on the path"}
+    config_exec = {}  # how this arm runs the workload (not part of the workload: both arms print the same `config`)
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -267,8 +274,8 @@ def main():
         dev.append(d)
         pinned.append({k: torch.from_numpy(a).pin_memory() for k, a in (("v", f["model"]["vmap4"]), ("n", f["model"]["nmap4"]),
                                                                           ("mi", f["model"]["rgba"]), ("d", f["live"]["depth"]), ("li", f["live"]["rgba"]))})
-    config["ring_frames"] = ring
-    config["cache"] = f"inputs cycle through {ring} distinct resident frames = {ring * per_frame_in / 1e6:.0f} MB (> 126 MB L2)"
+    config_exec["ring_frames"] = ring
+    config_exec["cache"] = f"inputs cycle through {ring} distinct resident frames = {ring * per_frame_in / 1e6:.0f} MB (> 126 MB L2)"
 
     props = torch.cuda.get_device_properties(local_rank)
     sms = props.multi_processor_count
@@ -282,7 +289,7 @@ def main():
         hs, ss = [], []
         for k in range(depth):
             h = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank)
-            threads = args.threads if depth > 1 else 0  # a tracker that owns the GPU keeps one 1024-thread block per SM
+            threads = args.threads if depth > 1 else 0  # a tracker that owns the GPU keeps the library default (one 768-thread block per SM)
             if threads:
                 h.set_block(threads)
             per_sm = max(1, 1024 // threads) if threads else 1
@@ -426,15 +433,16 @@ def main():
         # aggregate rate of the kernel is depth launches per k_ms
         achieved = depth * alg / (k_ms * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": "k_track (persistent cooperative: derivatives + SO3 + 3-level GN incl. solves)", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic_of(args.workload), "peak_source": peak_src,
+                "frac_step_anchored": alg / ((ms / steps) * 1e-3) / 1e9 / peak,  # algorithmic bytes of one frame's k_track / wall time per frame: no concurrency factor
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": k_ms, "concurrent_launches": depth,
                 "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
     depth = max(1, args.pipeline)
-    _thr = args.threads if args.threads else 1024
+    _thr = args.threads if args.threads else 768
     _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, 8)
-    config["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
+    config_exec["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
                           if depth > 1 else "single tracker, frames strictly one after another")
     native = depth > 1 and args.driver == "native" and share_rgb
     seq = None
@@ -443,11 +451,11 @@ def main():
         seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth, block_threads=args.threads,
                               grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
                               fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
-        config["driver"] = "dms_sequence_run (native host threads)"
+        config_exec["driver"] = "dms_sequence_run (native host threads)"
         pipe = None
         ms, ktimes, iters_seen, so3_seen, clocks, last = timed_native(seq, args.steps, args.warmup, False)
     else:
-        config["driver"] = "python threads over the per-call C ABI"
+        config_exec["driver"] = "python threads over the per-call C ABI"
         pipe = make_pipe(depth)
         ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
     value = world * args.steps / (ms * 1e-3)
@@ -456,7 +464,7 @@ def main():
     roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, 8) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
 
     if args.quick:
-        emit({"value": value, "roofline": roofline, "config": config, "clocks": clocks})
+        emit({"value": value, "roofline": roofline, "config": config, "config_exec": config_exec, "clocks": clocks})
         return
     e2e_steps = min(args.steps, 300)
     ms_e2e, _, _, _, _, last_e2e = timed_native(seq, e2e_steps, min(args.warmup, 5), True) if native else timed(pipe, e2e_steps, min(args.warmup, 5), True)
@@ -465,7 +473,7 @@ def main():
 
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": config, "roofline": roofline,
+           "config": config, "config_exec": config_exec, "roofline": roofline,
            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + (0 if (share_rgb and depth > 1) else frames[0]["live"]["rgba"].nbytes),
                    "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps, "last_frame_abs_translation_error_m": pose_err_e2e,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
@@ -480,21 +488,24 @@ def main():
         full = multi.gather_records({rank: rec[None]}, world, 1, device="cuda")
         if rank == 0:
             out["gathered_result_records"] = list(full.shape)
-    if depth > 1 and world == 1:
-        # the same sequence on one tracker owning the whole GPU: per-frame latency and the full-GPU kernel roofline
+    if depth > 1:
+        # Latency regime: the same sequence on ONE tracker that owns the GPU, one frame in flight (what a frame-to-model
+        # caller sees, ElasticFusion.cpp:173-201: the model view of frame f+1 exists only after frame f is fused).  Every
+        # rank measures it on its own GPU; rank 0 reports its own numbers.
         del pipe, seq
         pipe1 = make_pipe(1)
-        ms1, k1, it1, s31, _, _ = timed(pipe1, min(args.steps, 300), args.warmup, False)
         n1 = min(args.steps, 300)
+        ms1, k1, it1, s31, _, _ = timed(pipe1, n1, args.warmup, False)
         lat = np.sort(np.array(timed.latencies))
         ph = {k: float(np.mean([p_[k] for p_ in timed.phases])) * 1e3 for k in timed.phases[0]}
         gn_its = max(1, int(np.mean([sum(it) for it in it1])))
-        out["single_tracker"] = {"value": n1 / (ms1 * 1e-3), "unit": "frames/s", "latency_ms_per_frame": ms1 / n1,
-                                 "host_latency_ms": {"p50": float(lat[len(lat) // 2]), "p99": float(lat[min(len(lat) - 1, int(len(lat) * 0.99))]),
-                                                     "max": float(lat[-1]), "frames": int(len(lat))},
-                                 "track_us": ph.get("track"), "phase_us": ph,
-                                 "us_per_gn_iteration": (ph.get("icpStep", 0.0) + ph.get("rgbStep", 0.0) + ph.get("computeRgbResidual", 0.0)) / gn_its,
-                                 "roofline": roofline_of(ms1, n1, k1, it1, s31, 1)}
+        out["latency"] = {"value": world * n1 / (ms1 * 1e-3), "unit": "frames/s", "ms_per_frame": ms1 / n1, "frames": n1,
+                          "mode": "one tracker per GPU, one frame in flight, inputs resident in HBM",
+                          "host_latency_ms": {"p50": float(lat[len(lat) // 2]), "p99": float(lat[min(len(lat) - 1, int(len(lat) * 0.99))]),
+                                              "max": float(lat[-1]), "frames": int(len(lat))},
+                          "track_us": ph.get("track"), "phase_us": ph,
+                          "us_per_gn_iteration": (ph.get("icpStep", 0.0) + ph.get("rgbStep", 0.0) + ph.get("computeRgbResidual", 0.0)) / gn_its,
+                          "roofline": roofline_of(ms1, n1, k1, it1, s31, 1)}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         host_frames = frames[: min(ring, 4)]

@@ -150,6 +150,7 @@ SIGNATURES = {
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),
+    "dms_threshold_equiv": (None, [C.c_float, C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
 }
 
 _lib = None

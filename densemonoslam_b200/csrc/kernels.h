@@ -64,6 +64,7 @@ static const int MAX_DBG = 1024;
 
 void threshold_equiv(float distThres, float angleThres, float* dist2Max, float* sine2Lim);
 int track_block_threads_max();
+int track_block_threads_default();
 int track_max_grid(int device, int tpb);  // co-resident CTAs of tpb threads for the cooperative launch
 cudaError_t launch_track(const TrackParams& p, int grid, int tpb, cudaStream_t s);
 

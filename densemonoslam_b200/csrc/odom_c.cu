@@ -126,6 +126,13 @@ int dms_device_count(void) {
 
 size_t dms_track_d2h_bytes(void) { return sizeof(Ctrl); }
 
+void dms_threshold_equiv(float distThresh, float angleThresh, float* dist2Max, float* sine2Lim) {
+  float d = 0.f, a = 0.f;
+  threshold_equiv(distThresh, angleThresh, &d, &a);
+  if (dist2Max) *dist2Max = d;
+  if (sine2Lim) *sine2Lim = a;
+}
+
 const char* dms_odom_last_error(const dms_odom* h) { return h ? h->err.c_str() : "null handle"; }
 
 int dms_odom_create(dms_odom** out, int device, int width, int height, float cx, float cy, float fx, float fy, float distThresh,
@@ -208,10 +215,10 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_done, cudaEventBlockingSync | cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { dms_odom_destroy(h); return (int)e; }
-  h->tpb = track_block_threads_max();
+  h->tpb = track_block_threads_default();
   if (const char* g = getenv("DMS_TRACK_THREADS")) {  // tuning knob: smaller CTAs (several co-resident per SM)
     const int v = atoi(g);
-    if (v >= 64 && v <= h->tpb && (v & 31) == 0) h->tpb = v;
+    if (v >= 64 && v <= track_block_threads_max() && (v & 31) == 0) h->tpb = v;
   }
   h->grid = track_max_grid(device, h->tpb);
   if (h->grid <= 0) { dms_odom_destroy(h); return DMS_ERR_DEVICE; }
@@ -251,7 +258,7 @@ int dms_odom_set_grid(dms_odom* h, int n_ctas) {
 }
 int dms_odom_set_block(dms_odom* h, int threads) {
   if (!h || threads < 0) return DMS_ERR_INVALID;
-  const int tpb = threads == 0 ? track_block_threads_max() : threads;
+  const int tpb = threads == 0 ? track_block_threads_default() : threads;
   cudaSetDevice(h->device);
   const int g = track_max_grid(h->device, tpb);
   if (g <= 0) return DMS_ERR_INVALID;

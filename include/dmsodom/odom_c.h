@@ -75,7 +75,7 @@ const char* dms_odom_last_error(const dms_odom* h);
  * concurrently on one GPU, each on its own stream: the barrier / solve latency of one overlaps the pixel phases of
  * the others.  Results do not depend on the limit (the reduction is order-free). */
 int dms_odom_set_grid(dms_odom* h, int n_ctas);
-/* Threads per thread block of the tracking kernel (multiple of 32 in [64, 1024]; 0 = 1024).  With 512 or fewer, two or
+/* Threads per thread block of the tracking kernel (multiple of 32 in [64, 1024]; 0 = the default, 768).  With 512 or fewer, two or
  * more blocks (of different handles) are resident per SM, so one tracker's pixel phases fill the issue slots another
  * leaves idle at its barriers.  Resets the grid limit to "all" when it no longer fits.  Results do not depend on it. */
 int dms_odom_set_block(dms_odom* h, int threads);
@@ -212,14 +212,15 @@ int dms_depth_metric(const uint16_t* d_raw, size_t pitch_in, int rows, int cols,
  * engine's frame loop with a memory budget fixed at start-up, a real-time thread that cannot take
  * cudaMalloc's implicit device-wide synchronisation, or a plug-in that only ever works on buffers it
  * is handed.  It needs no handle: the caller passes the four planar maps (3*rows x cols floats each,
- * x plane rows first, row pitch `pitch_bytes`, 16-byte aligned rows), the level intrinsics, the
+ * x plane rows first, row pitch `pitch_bytes` a multiple of 4), the level intrinsics, the
  * poses as in dms_odom_icp_step, and a DEVICE record `d_out` that receives the same 27 products +
  * residual and the inlier count.  The work is enqueued on `stream`; nothing is copied to the host.
  *
  * The reduction's scratch (the exact-accumulator lines, 24 KB) is a static device array inside
  * the library, present on every GPU that loads it until the process exits.  Consequences:
  *  - the call performs no cudaMalloc / cudaFree and uses no allocating library routine;
- *  - images above DMS_NOALLOC_MAX_PIXELS are refused with DMS_ERR_TOO_LARGE (and a line on stderr);
+ *  - images above DMS_NOALLOC_MAX_PIXELS pixels, or with more than DMS_NOALLOC_MAX_DIM rows or columns (the same
+ *    per-dimension limit as dms_odom_create), are refused with DMS_ERR_TOO_LARGE (and a line on stderr);
  *  - all calls on one GPU share the array, which is cleared at the start of every call: two calls
  *    whose GPU work overlaps (different streams, or different host threads) race on it and give
  *    wrong sums -- serialise them;
@@ -227,6 +228,7 @@ int dms_depth_metric(const uint16_t* d_raw, size_t pitch_in, int rows, int cols,
  *    with that device current); make that first call before starting any stream capture.
  * Results are bit-identical to dms_odom_icp_step on the same inputs. */
 #define DMS_NOALLOC_MAX_PIXELS (1 << 24)
+#define DMS_NOALLOC_MAX_DIM 16384
 typedef struct dms_step_sums {
   float vals[28];     /* 27 products in JtJJtrSE3 order (types.cuh:117-131), then the squared residual */
   int64_t count;      /* inliers */
@@ -242,6 +244,10 @@ int dms_icp_step_noalloc(const float* d_vmap_curr, const float* d_nmap_curr, con
 /* ---- library info */
 const char* dms_version(void);
 int dms_device_count(void);
+/* Host-side helper, exposed for tests: the squared-domain equivalents of the two ICP acceptance tests of reduce.cu:301
+ * (sqrtf(d2) <= distThresh  <=>  d2 <= *dist2Max;  sqrtf(s2) < angleThresh  <=>  s2 < *sine2Lim), exact for every float
+ * threshold including infinities.  Needs no GPU. */
+void dms_threshold_equiv(float distThresh, float angleThresh, float* dist2Max, float* sine2Lim);
 /* bytes copied device->host by one dms_odom_track call (the control block with pose + public fields) */
 size_t dms_track_d2h_bytes(void);
 

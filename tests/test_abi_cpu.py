@@ -74,3 +74,25 @@ def test_headers_compile_as_c_and_cpp(tmp_path):
         f.write_text(src)
         r = subprocess.run([comp, std, "-Wall", "-Werror", "-fsyntax-only", "-I", inc, str(f)], capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
+
+
+def test_threshold_equivalents_for_every_kind_of_threshold():
+    """The squared-domain thresholds must terminate and be exact for ordinary, huge and infinite thresholds (a caller may
+    pass +inf to switch a test off)."""
+    import ctypes as C
+    import numpy as np
+    from densemonoslam_b200 import _lib
+    L = _lib.load()
+    f32 = np.float32
+    for T in (0.0, 1e-30, 0.1, 0.3420201, 1.0, 12345.678, 1e19, 3e19, float(np.finfo(f32).max), float("inf")):
+        d, a = C.c_float(), C.c_float()
+        L.dms_threshold_equiv(T, T, C.byref(d), C.byref(a))
+        d, a, T32 = f32(d.value), f32(a.value), f32(T)
+        with np.errstate(over="ignore", invalid="ignore"):
+            # d = the largest float whose sqrt is <= T; a = the smallest float whose sqrt is >= T
+            assert np.sqrt(d) <= T32 and (np.isinf(d) or not np.sqrt(np.nextafter(d, f32(np.inf))) <= T32), (T, d)
+            if T > 0:
+                assert (np.isinf(a) or np.sqrt(a) >= T32) and (a == 0 or np.sqrt(np.nextafter(a, f32(0))) < T32), (T, a)
+    d, a = C.c_float(), C.c_float()
+    L.dms_threshold_equiv(float("nan"), -1.0, C.byref(d), C.byref(a))
+    assert d.value < 0 and a.value == 0   # nothing passes

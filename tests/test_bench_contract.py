@@ -35,7 +35,12 @@ def test_our_arm_line():
     assert BASE_KEYS | {"roofline", "gpu_launches", "clocks"} <= set(j)
     assert j["n_gpus"] == 1 and j["steps"] == 16 and j["warmup"] == 3 and j["vs_baseline"] is None and j["dtype"] == "f32"
     r = j["roofline"]
-    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9 and r["traffic"] > 0
+    assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    assert r["traffic"] is None or r["traffic"] > 0          # from the committed ncu summary of this workload, null without one
+    assert 0 < r["frac_step_anchored"] < 1
+    assert set(j["config"]) == {"workload", "width", "height", "icpWeight", "iterations", "so3", "parallelism"}   # same keys in both arms
+    lat = j["latency"]
+    assert lat["value"] > 0 and lat["host_latency_ms"]["p50"] > 0 and lat["roofline"]["concurrent_launches"] == 1
     e = j["e2e"]
     assert e["value"] > 0 and e["h2d_bytes_per_step"] > 15e6 and e["d2h_bytes_per_step"] > 0 and e["value"] != j["value"]
     assert j["gpu_launches"] == 5 * 16 + 1 and j["value"] > 0 and "workload" in j["config"]

@@ -211,6 +211,7 @@ FLAG_ROWS = {
     "rgbOnly": (True, 10.0, True, False, True, False),
     "icpOnly_w100": (False, 100.0, True, False, False, False),
     "gputest": (False, 10.0, False, False, True, False),
+    "referenceFrame": (False, 10.0, True, False, True, True),   # ReferenceFrame.h:82-90: ICP + RGB, so3, interMap => 50/50/50
 }
 
 
@@ -231,6 +232,52 @@ def test_full_track_parity_vga(torch_cuda, orc, synth, pair_vga, row):
     for l in range(3):
         assert np.array_equal(g.download("nextImage", l), o.buffer("nextImage", l))
         assert np.array_equal(g.download("lastNextImage", l), o.buffer("lastNextImage", l))
+
+
+def test_reference_frame_call_shape(torch_cuda, orc, synth, pair_vga):
+    """ReferenceFrame::m_rgbd (ReferenceFrame.h:82-90; usage matrix row 4 of SURVEY 8b): full resolution, initICPModel ->
+    initICP(V, N) -> initRGBModel -> initRGB, so BOTH depth pyramids come from the second vertex map (RO.cpp:213,240,246),
+    then ICP + RGB with SO(3) and interMap = 150 Gauss-Newton iterations, every one compared."""
+    cam, model, live, T = pair_vga
+    g, o = both(orc, synth, cam)
+    pose = np.eye(4, dtype=np.float32)
+    cv = lambda a: to_dev(torch_cuda, a)
+    g.initFirstRGB(cv(model["rgba"])); o.initFirstRGB(model["rgba"])
+    g.initICPModel(cv(model["vmap4"]), cv(model["nmap4"]), 25.0, pose); o.initICPModel(model["vmap4"], model["nmap4"], pose)
+    g.initICP(cv(live["vmap4"]), cv(live["nmap4"]), 25.0); o.initICPMaps(live["vmap4"], live["nmap4"])
+    g.initRGBModel(cv(model["rgba"])); o.initRGBModel(model["rgba"])
+    g.initRGB(cv(live["rgba"])); o.initRGB(live["rgba"])
+    check_pyramids(g, o)
+    compare_track(g, o, pose[:3, 3], pose[:3, :3], FLAG_ROWS["referenceFrame"])
+    assert g.iters == [50, 50, 50] and len(g.trace()) == 150
+
+
+def mat3_inv_f32(m):
+    """Eigen's fixed-size 3x3 .inverse() by cofactors in fp32, in the operation order the library and the oracle use."""
+    m = [np.float32(x) for x in np.asarray(m, np.float32).reshape(9)]
+    c00 = m[4] * m[8] - m[5] * m[7]; c01 = m[5] * m[6] - m[3] * m[8]; c02 = m[3] * m[7] - m[4] * m[6]
+    det = m[0] * c00 + m[1] * c01 + m[2] * c02
+    i = np.float32(1) / det
+    return np.array([c00 * i, (m[2] * m[7] - m[1] * m[8]) * i, (m[1] * m[5] - m[2] * m[4]) * i,
+                     c01 * i, (m[0] * m[8] - m[2] * m[6]) * i, (m[2] * m[3] - m[0] * m[5]) * i,
+                     c02 * i, (m[1] * m[6] - m[0] * m[7]) * i, (m[0] * m[4] - m[1] * m[3]) * i], np.float32).reshape(3, 3)
+
+
+def test_icp_residual_against_oracle(torch_cuda, orc, synth, pair_small):
+    """getICPResidual (RO.cpp:612-643): level-0 residual-only ICP with the reference's odd argument shape -- rot_curr.inverse()
+    as Rprev_inv and trans_prev unchanged (RO.cpp:623-625) -- against the oracle's icpStep on the same arguments."""
+    from densemonoslam_b200.odometry import DEFAULT_ANGLE_THRESH
+    cam, model, live, T = pair_small
+    g, o = both(orc, synth, cam)
+    pose = synth.pose_from((0.01, -0.02, 0.015), (0.03, 0.01, -0.02)).astype(np.float32)
+    load_frame_to_model(torch_cuda, g, o, model, live, pose)
+    Tc = (pose.astype(np.float64) @ synth.pose_from((0.004, -0.006, 0.003), (0.008, -0.004, 0.006))).astype(np.float32)
+    Rc, tc = np.ascontiguousarray(Tc[:3, :3]), np.ascontiguousarray(Tc[:3, 3])
+    err, cnt = g.getICPResidual(tc, Rc, pose[:3, 3], pose[:3, :3])
+    p, inl = orc.icp_step(Rc, tc, o.buffer("vmap_curr", 0), o.buffer("nmap_curr", 0), mat3_inv_f32(Rc), pose[:3, 3], (cam.fx, cam.fy, cam.cx, cam.cy),
+                          o.buffer("vmap_g_prev", 0), o.buffer("nmap_g_prev", 0), 0.10, DEFAULT_ANGLE_THRESH)
+    assert cnt == inl and inl > 1000
+    assert np.float32(err) == np.sqrt(np.float32(p[27])) / np.float32(inl)
 
 
 def test_full_track_parity_kitti_shape(torch_cuda, orc, synth):
@@ -268,7 +315,7 @@ def test_identity_motion_and_covariance(torch_cuda, orc, synth, pair_small):
     cov_o = orc.covariance(g.lastA)
     assert np.allclose(g.getCovariance(), cov_o, rtol=1e-9, atol=1e-12)
     err, cnt = g.getICPResidual(t, R, pose[:3, 3], pose[:3, :3])
-    assert cnt > 0 and np.isfinite(err)
+    assert cnt > 0 and np.isfinite(err)   # compared with the oracle in test_icp_residual_against_oracle
 
 
 def test_stopwatch_keys(torch_cuda, orc, synth, pair_small):
@@ -277,29 +324,25 @@ def test_stopwatch_keys(torch_cuda, orc, synth, pair_small):
     pose = np.eye(4, dtype=np.float32)
     load_frame_to_model(torch_cuda, g, o, model, live, pose)
     g.initFirstRGB(to_dev(torch_cuda, model["rgba"]))
-    g.set_timing(True)
+    g.set_timing(1)
     g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["frameToModel"])
     tm = g.timing()
     assert set(tm) >= {"icpStep", "rgbStep", "computeRgbResidual", "so3Step"}  # GPUTest.cpp:280-283 reads these
     assert tm["track"] > 0 and tm["icpStep"] > 0 and tm["rgbStep"] > 0 and tm["so3Step"] > 0
 
 
-def test_large_frame_properties_1080p(torch_cuda, orc, synth):
-    """Full-size property checks that do not need the oracle at 1920x1080: determinism (two runs give
-    bit-identical traces) and invariance of the reduction to the launch schedule is implied by it."""
+def test_full_track_parity_1080p(torch_cuda, orc, synth):
+    """configs[3]: 1920x1080, full pyramid, every iteration against the oracle; the second run on the same handle must
+    reproduce the first bit for bit (the reduction does not depend on the launch schedule)."""
     cam = synth.CAM_1080P
     model, live, T = synth.frame_pair(cam, seed=99)
-    from densemonoslam_b200.odometry import RGBDOdometry
-    g = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy)
-    g.set_trace(True)
+    g, o = both(orc, synth, cam)
     pose = np.eye(4, dtype=np.float32)
-    cv = lambda a: to_dev(torch_cuda, a)
     runs = []
     for _ in range(2):
-        g.initFirstRGB(cv(model["rgba"]))
-        g.initICPModel(cv(model["vmap4"]), cv(model["nmap4"]), 25.0, pose); g.initRGBModel(cv(model["rgba"]))
-        g.initICP(cv(live["depth"]), 25.0); g.initRGB(cv(live["rgba"]))
-        t, R = g.getIncrementalTransformation(pose[:3, 3], pose[:3, :3], *FLAG_ROWS["frameToModel"])
+        g.initFirstRGB(to_dev(torch_cuda, model["rgba"])); o.initFirstRGB(model["rgba"])
+        load_frame_to_model(torch_cuda, g, o, model, live, pose)
+        t, R = compare_track(g, o, pose[:3, 3], pose[:3, :3], FLAG_ROWS["frameToModel"])
         runs.append((t, R, g.trace()))
     (t0, R0, tr0), (t1, R1, tr1) = runs
     assert np.array_equal(t0, t1) and np.array_equal(R0, R1)

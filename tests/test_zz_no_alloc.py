@@ -20,7 +20,7 @@ from conftest import assert_f32_equal
 pytestmark = pytest.mark.gpu
 
 
-def test_noalloc_icp_step_matches_handle_entry_point_twice(synth):
+def test_noalloc_icp_step_matches_handle_entry_point_twice(synth, orc):
     import torch
     assert torch.cuda.is_available()
     from densemonoslam_b200 import _lib
@@ -58,9 +58,20 @@ def test_noalloc_icp_step_matches_handle_entry_point_twice(synth):
         assert out.bad == 0
         assert out.count == ref_cnt and ref_cnt > 1000
         assert_f32_equal(np.array(out.vals[:], np.float32), ref, f"level {level}")
+        # ... and the CPU oracle's icpStep on the same maps (the handle-based entry point is itself checked against it elsewhere)
+        maps = {n: g.download(n, level) for n in ("vmap_curr", "nmap_curr", "vmap_g_prev", "nmap_g_prev")}
+        o_vals, o_cnt = orc.icp_step(Rc, tc, maps["vmap_curr"], maps["nmap_curr"], Rprev_inv, tprev, (cam.fx / div, cam.fy / div, cam.cx / div, cam.cy / div),
+                                     maps["vmap_g_prev"], maps["nmap_g_prev"], 0.10, DEFAULT_ANGLE_THRESH)
+        assert out.count == o_cnt
+        assert_f32_equal(np.array(out.vals[:], np.float32), o_vals, f"level {level} vs oracle")
 
     # beyond the stated maximum: refused before any GPU work
     rc = L.dms_icp_step_noalloc(ptr["vmap_curr"], ptr["nmap_curr"], ptr["vmap_g_prev"], ptr["nmap_g_prev"], 1 << 20, 8192, 4096,
                                 1.0, 1.0, 0.0, 0.0, fp(Rc), fp(tc), fp(Rprev_inv), fp(tprev), 0.10, DEFAULT_ANGLE_THRESH,
                                 C.c_void_p(d_out.data_ptr()), None)
     assert rc == -4  # DMS_ERR_TOO_LARGE
+    # a frame within the pixel limit but wider than 16384 columns is refused too (the row index arithmetic is only exact up to there)
+    rc = L.dms_icp_step_noalloc(ptr["vmap_curr"], ptr["nmap_curr"], ptr["vmap_g_prev"], ptr["nmap_g_prev"], 1 << 27, 2, 8000000,
+                                1.0, 1.0, 0.0, 0.0, fp(Rc), fp(tc), fp(Rprev_inv), fp(tprev), 0.10, DEFAULT_ANGLE_THRESH,
+                                C.c_void_p(d_out.data_ptr()), None)
+    assert rc == -4
