@@ -86,6 +86,7 @@ SIGNATURES = {
     "dms_odom_set_grid": (C.c_int, [_P, C.c_int]),
     "dms_odom_set_block": (C.c_int, [_P, C.c_int]),
     "dms_odom_set_wait": (C.c_int, [_P, C.c_int]),
+    "dms_odom_set_numerics": (C.c_int, [_P, C.c_int]),
     "dms_odom_set_timing": (C.c_int, [_P, C.c_int]),
     "dms_odom_get_timing": (C.c_int, [_P, C.POINTER(DmsTiming)]),
     "dms_odom_init_icp_depth": (C.c_int, [_P, _P, C.c_size_t, C.c_float, _P]),

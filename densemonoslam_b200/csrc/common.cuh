@@ -59,6 +59,23 @@ __device__ __forceinline__ float3 normalized3(float3 a) {
   const float rn = fdiv(1.0f, fsqrt(dot3(a, a)));
   return make_float3(fmul(a.x, rn), fmul(a.y, rn), fmul(a.z, rn));
 }
+// ------------------------------------------------------------------ legacy numerics (dms_odom_set_numerics)
+// The reference is built with --ftz=true --prec-div=false --prec-sqrt=false (Core/src/CMakeLists.txt:48-49): nvcc turns
+// its a / b into div.full.ftz.f32, 1.0f / a into rcp.approx.ftz.f32, sqrtf into sqrt.approx.ftz.f32, rsqrtf into
+// rsqrt.approx.ftz.f32 and x / 1000.f into a multiplication by 0.001f.  These helpers issue exactly those PTX
+// instructions, so a kernel instantiated with LEG = true rounds like the reference's own build at the sites where a
+// division or square root feeds a truncation, a pixel rounding or a threshold test (the CPU cannot reproduce the MUFU
+// approximations; the GPU can, bit for bit).  LEG = false is the IEEE arithmetic the CPU oracle restates.
+__device__ __forceinline__ float div_full_ftz(float a, float b) { float r; asm("div.full.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ float rcp_approx_ftz(float a) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float sqrt_approx_ftz(float a) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+__device__ __forceinline__ float rsqrt_approx_ftz(float a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+template <bool LEG> __device__ __forceinline__ float div_t(float a, float b) { return LEG ? div_full_ftz(a, b) : fdiv(a, b); }
+template <bool LEG> __device__ __forceinline__ float3 normalized3_t(float3 a) {  // operators.cuh:82-86
+  const float rn = LEG ? rsqrt_approx_ftz(dot3(a, a)) : fdiv(1.0f, fsqrt(dot3(a, a)));
+  return make_float3(fmul(a.x, rn), fmul(a.y, rn), fmul(a.z, rn));
+}
+
 __device__ __forceinline__ float3 mul33(const Mat33& m, float3 a) { return make_float3(dot3(m.r[0], a), dot3(m.r[1], a), dot3(m.r[2], a)); }
 
 // ------------------------------------------------------------------ exact accumulation

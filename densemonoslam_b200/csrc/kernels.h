@@ -9,9 +9,9 @@ namespace dms {
 
 // ---- pyramid.cu
 cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4, const float4* n4, int pitch4,
-                                const float* pose16_or_null, float* zdepth, float zcut, cudaStream_t s);
-cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, cudaStream_t s);
-cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, cudaStream_t s);
+                                const float* pose16_or_null, float* zdepth, float zcut, bool legacy, cudaStream_t s);
+cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, bool legacy, cudaStream_t s);
+cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, bool legacy, cudaStream_t s);
 
 cudaError_t launch_depth_bilateral(const unsigned short* src, int sp, unsigned short* dst, int dp, int rows, int cols, float maxD, cudaStream_t s);
 cudaError_t launch_depth_metric(const unsigned short* src, int sp, float* dst, int dp, int rows, int cols, float maxD, cudaStream_t s);
@@ -50,6 +50,7 @@ struct TrackParams {
   float icpWeight;
   float Rprev[9], tprev[3], Rprev_inv[9];
   float dist2Max, sine2Lim;  // squared-domain equivalents of distThres / angleThres (threshold_equiv)
+  float distThres, angleThres;
   int iters[3];
   double Kd[3][9], Kinv[3][9];  // level intrinsics matrix and its inverse (RO.cpp:415-421, K.inverse())
   Ctrl* ctrl;
@@ -66,18 +67,18 @@ void threshold_equiv(float distThres, float angleThres, float* dist2Max, float* 
 int track_block_threads_max();
 int track_block_threads_default();
 int track_max_grid(int device, int tpb);  // co-resident CTAs of tpb threads for the cooperative launch
-cudaError_t launch_track(const TrackParams& p, int grid, int tpb, cudaStream_t s);
+cudaError_t launch_track(const TrackParams& p, int grid, int tpb, bool legacy, cudaStream_t s);
 
 // single-step operators (regular launches + finalize)
 struct StepOut { float vals[28]; long long count, count2, sigma; int bad; int pad; };
 cudaError_t launch_derivatives(const Level* lv, cudaStream_t s);
 cudaError_t launch_icp_step(const Level& lv, const float Rcurr[9], const float tcurr[3], const float Rprev_inv[9],
                             const float tprev[3], float distThres, float angleThres, unsigned long long* acc, StepOut* d_out,
-                            unsigned char* d_mask_or_null, int mask_pitch, cudaStream_t s);
+                            unsigned char* d_mask_or_null, int mask_pitch, bool legacy, cudaStream_t s);
 cudaError_t launch_rgb_residual(const Level& lv, const float kt[3], const float krkinv[9], unsigned long long* acc,
-                                StepOut* d_out, cudaStream_t s);
-cudaError_t launch_rgb_step(const Level& lv, float sigma, unsigned long long* acc, StepOut* d_out, cudaStream_t s);
+                                StepOut* d_out, bool legacy, cudaStream_t s);
+cudaError_t launch_rgb_step(const Level& lv, float sigma, unsigned long long* acc, StepOut* d_out, bool legacy, cudaStream_t s);
 cudaError_t launch_so3_step(const Level& lv, const float H[9], const float kinv[9], const float krlr[9],
-                            unsigned long long* acc, StepOut* d_out, cudaStream_t s);
+                            unsigned long long* acc, StepOut* d_out, bool legacy, cudaStream_t s);
 
 }  // namespace dms

@@ -232,7 +232,7 @@ int dms_nid_set_keyframe(dms_nid* h, const float* v4, const uint8_t* rgba, const
   for (int which = 0; which < 2; ++which) {
     k_vertices_to_depth<<<grid, 256, 0, s>>>((const float4*)(which ? old_v4 : v4), h->height, h->width, depthCutoff, h->zsrc, h->lv[0].pitch_f32);
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = launch_populate(h->lv, which, h->zsrc, (const uchar4*)(which ? old_rgba : rgba), h->width * 4, s);
+    if (e == cudaSuccess) e = launch_populate(h->lv, which, h->zsrc, (const uchar4*)(which ? old_rgba : rgba), h->width * 4, false, s);
     if (e != cudaSuccess) return (int)e;
   }
   h->have_keyframe = 1;

@@ -39,6 +39,7 @@ struct dms_odom {
   int grid, grid_max;    // CTAs of the cooperative tracking kernel in use / co-resident maximum
   int tpb;               // threads per CTA of the tracking kernel
   int timing, tracing;
+  int legacy;            // dms_odom_set_numerics: 1 = the reference build's approximate division / square roots
   dms_odom_result last;  // public fields of the last track call
   dms_odom_timing last_timing;
   cudaEvent_t ev0, ev1;
@@ -98,7 +99,7 @@ int populate(dms_odom* h, const uint8_t* d_rgba, size_t pitch, int which, cudaSt
     CK(cudaStreamWaitEvent(s, h->wait_reader, 0));
     h->wait_reader = nullptr;
   }
-  CK(launch_populate(h->lv, which, h->zdepth, reinterpret_cast<const uchar4*>(d_rgba), (int)pitch, s));
+  CK(launch_populate(h->lv, which, h->zdepth, reinterpret_cast<const uchar4*>(d_rgba), (int)pitch, h->legacy != 0, s));
   return DMS_OK;
 }
 
@@ -146,7 +147,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
   h->distThres = distThresh; h->angleThres = angleThresh;
   h->slab = nullptr; h->stage_v4 = h->stage_n4 = nullptr; h->stage_rgba = nullptr; h->stage_depth = nullptr;
   h->h_ctrl = nullptr; h->h_step = nullptr; h->timing = 0; h->tracing = 0; h->ev0 = h->ev1 = nullptr;
-  h->in_flight = 0; h->track_stream = nullptr; h->blocking_wait = 0; h->wait_ema_us = 0.0; h->wait_reader = nullptr;
+  h->legacy = 0; h->in_flight = 0; h->track_stream = nullptr; h->blocking_wait = 0; h->wait_ema_us = 0.0; h->wait_reader = nullptr;
   h->ev_rgb = h->ev_took = h->ev_done = nullptr; h->rgb_pyr[0] = h->rgb_pyr[1] = h->rgb_pyr[2] = nullptr;
   memset(&h->last, 0, sizeof h->last); memset(&h->last_timing, 0, sizeof h->last_timing);
   // RO.cpp:26-31 initial public state
@@ -268,6 +269,7 @@ int dms_odom_set_block(dms_odom* h, int threads) {
   return DMS_OK;
 }
 int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 3) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
+int dms_odom_set_numerics(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 1) return DMS_ERR_INVALID; h->legacy = mode; return DMS_OK; }
 int dms_odom_set_timing(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 2) return DMS_ERR_INVALID; h->timing = mode; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 
@@ -277,7 +279,7 @@ int dms_odom_init_icp_depth(dms_odom* h, const uint16_t* d_depth, size_t pitch, 
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
   if (pitch == 0) pitch = (size_t)h->width * 2;
-  CK(launch_icp_depth(h->lv, d_depth, (int)pitch, depthCutoff, s));
+  CK(launch_icp_depth(h->lv, d_depth, (int)pitch, depthCutoff, h->legacy != 0, s));
   return DMS_OK;
 }
 
@@ -287,7 +289,7 @@ int dms_odom_init_icp_maps(dms_odom* h, const float* d_v4, const float* d_n4, si
   Bind b(h->device);
   if (pitch == 0) pitch = (size_t)h->width * 16;
   CK(launch_maps_pyramid(h->lv, false, reinterpret_cast<const float4*>(d_v4), reinterpret_cast<const float4*>(d_n4), (int)pitch, nullptr,
-                         h->zdepth, 6.0f, (cudaStream_t)stream));
+                         h->zdepth, 6.0f, h->legacy != 0, (cudaStream_t)stream));
   return DMS_OK;
 }
 
@@ -298,7 +300,7 @@ int dms_odom_init_icp_model(dms_odom* h, const float* d_v4, const float* d_n4, s
   Bind b(h->device);
   if (pitch == 0) pitch = (size_t)h->width * 16;
   CK(launch_maps_pyramid(h->lv, true, reinterpret_cast<const float4*>(d_v4), reinterpret_cast<const float4*>(d_n4), (int)pitch, pose,
-                         h->zdepth, 6.0f, (cudaStream_t)stream));
+                         h->zdepth, 6.0f, h->legacy != 0, (cudaStream_t)stream));
   return DMS_OK;
 }
 
@@ -410,6 +412,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   memcpy(P.Rprev, rot, sizeof P.Rprev); memcpy(P.tprev, trans, sizeof P.tprev);
   mat3_inv_host<float>(P.Rprev, P.Rprev_inv);
   threshold_equiv(h->distThres, h->angleThres, &P.dist2Max, &P.sine2Lim);
+  P.distThres = h->distThres; P.angleThres = h->angleThres;
   P.iters[0] = interMap ? 50 : fastOdom ? 3 : 10;  // RO.cpp:387-389
   P.iters[1] = interMap ? 50 : pyramid ? 5 : 0;
   P.iters[2] = interMap ? 50 : pyramid ? 4 : 0;
@@ -425,7 +428,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
   P.seglist = h->seglist;
   if (h->timing >= 2) CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s));
   if (h->timing) CK(cudaEventRecord(h->ev0, s));
-  cudaError_t e = launch_track(P, h->grid, h->tpb, s);
+  cudaError_t e = launch_track(P, h->grid, h->tpb, h->legacy != 0, s);
   if (e != cudaSuccess) return fail(h, (int)e, "cooperative launch of k_track");
   if (h->timing) CK(cudaEventRecord(h->ev1, s));
   CK(cudaMemcpyAsync(h->h_ctrl, h->ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, s));
@@ -550,7 +553,7 @@ int dms_odom_icp_step(dms_odom* h, int level, const float Rcurr[9], const float 
   cudaStream_t s = (cudaStream_t)stream;
   const Level& L = h->lv[level];
   CK(launch_icp_step(L, Rcurr, tcurr, Rprev_inv, tprev, h->distThres, h->angleThres, h->step_acc, h->step_out, h_mask ? h->mask : nullptr,
-                     h->lv[0].pitch_u8, s));
+                     h->lv[0].pitch_u8, h->legacy != 0, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out28) memcpy(out28, h->h_step->vals, sizeof(float) * 28);
   if (inliers) *inliers = h->h_step->count;
@@ -562,7 +565,7 @@ int dms_odom_rgb_residual(dms_odom* h, int level, const float kt[3], const float
   if (!h || level < 0 || level > 2 || !kt || !krkinv) return fail(h, DMS_ERR_INVALID, "rgb_residual: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_rgb_residual(h->lv[level], kt, krkinv, h->step_acc, h->step_out, s));
+  CK(launch_rgb_residual(h->lv[level], kt, krkinv, h->step_acc, h->step_out, h->legacy != 0, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (count) *count = h->h_step->count;
   if (sigma) *sigma = h->h_step->sigma;
@@ -573,7 +576,7 @@ int dms_odom_rgb_step(dms_odom* h, int level, float sigma, float out28[28], int6
   if (!h || level < 0 || level > 2) return fail(h, DMS_ERR_INVALID, "rgb_step: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_rgb_step(h->lv[level], sigma, h->step_acc, h->step_out, s));
+  CK(launch_rgb_step(h->lv[level], sigma, h->step_acc, h->step_out, h->legacy != 0, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out28) memcpy(out28, h->h_step->vals, sizeof(float) * 28);
   if (count) *count = h->h_step->count;
@@ -585,7 +588,7 @@ int dms_odom_so3_step(dms_odom* h, int level, const float H[9], const float kinv
   if (!h || level < 0 || level > 2 || !H || !kinv || !krlr) return fail(h, DMS_ERR_INVALID, "so3_step: bad argument");
   Bind b(h->device);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(launch_so3_step(h->lv[level], H, kinv, krlr, h->step_acc, h->step_out, s));
+  CK(launch_so3_step(h->lv[level], H, kinv, krlr, h->step_acc, h->step_out, h->legacy != 0, s));
   int rc = fetch_step(h, s); if (rc) return rc;
   if (out10) memcpy(out10, h->h_step->vals, sizeof(float) * 10);
   if (count) *count = h->h_step->count;

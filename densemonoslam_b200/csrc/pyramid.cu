@@ -36,13 +36,14 @@ __device__ __forceinline__ float3 xform_n(const MapsPyrArgs& a, float3 n) {
 }
 
 // box average of 4 taps (cf.cu:459-486); NaN in any x tap -> invalid
+template <bool LEG>
 __device__ __forceinline__ float3 box4(float3 a, float3 b, float3 c, float3 d, bool normalize) {
   if (isnan(a.x) || isnan(b.x) || isnan(c.x) || isnan(d.x)) return make_float3(qnan(), qnan(), qnan());
   float3 n;
   n.x = fmul(fadd(fadd(fadd(a.x, b.x), c.x), d.x), 0.25f);
   n.y = fmul(fadd(fadd(fadd(a.y, b.y), c.y), d.y), 0.25f);
   n.z = fmul(fadd(fadd(fadd(a.z, b.z), c.z), d.z), 0.25f);
-  if (normalize) n = normalized3(n);
+  if (normalize) n = normalized3_t<LEG>(n);
   return n;
 }
 
@@ -57,7 +58,7 @@ __device__ __forceinline__ void store_plane3_pair(float* base, int pitch, int ro
 __device__ __forceinline__ float3 shfl3(float3 v, int src) {
   return make_float3(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src));
 }
-template <bool TRANSFORM>
+template <bool TRANSFORM, bool LEG>
 __global__ void __launch_bounds__(128) k_maps_pyramid(const MapsPyrArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int x1 = blockIdx.x * 32 + (warp & 1) * 16 + (lane & 15);   // level-1 pixel of this thread
@@ -89,8 +90,8 @@ __global__ void __launch_bounds__(128) k_maps_pyramid(const MapsPyrArgs a) {
       store_plane3(a.nmap[0], a.pitch[0], a.rows[0], y, x0, na);
     }
   }
-  const float3 vv = box4(v0[0], v0[1], v0[2], v0[3], false);
-  const float3 nn = box4(n0[0], n0[1], n0[2], n0[3], true);
+  const float3 vv = box4<LEG>(v0[0], v0[1], v0[2], v0[3], false);
+  const float3 nn = box4<LEG>(n0[0], n0[1], n0[2], n0[3], true);
   if (x1 < a.cols[1] && y1 < a.rows[1]) {
     store_plane3(a.vmap[1], a.pitch[1], a.rows[1], y1, x1, xform_v<TRANSFORM>(a, vv));
     store_plane3(a.nmap[1], a.pitch[1], a.rows[1], y1, x1, xform_n<TRANSFORM>(a, nn));
@@ -100,13 +101,13 @@ __global__ void __launch_bounds__(128) k_maps_pyramid(const MapsPyrArgs a) {
   const float3 nb = shfl3(nn, lane + 1), nc = shfl3(nn, lane + 16), nd = shfl3(nn, lane + 17);
   const int x2 = x1 >> 1, y2 = y1 >> 1;
   if ((lane & 17) == 0 && x2 < a.cols[2] && y2 < a.rows[2]) {
-    store_plane3(a.vmap[2], a.pitch[2], a.rows[2], y2, x2, xform_v<TRANSFORM>(a, box4(vv, vb, vc, vd, false)));
-    store_plane3(a.nmap[2], a.pitch[2], a.rows[2], y2, x2, xform_n<TRANSFORM>(a, box4(nn, nb, nc, nd, true)));
+    store_plane3(a.vmap[2], a.pitch[2], a.rows[2], y2, x2, xform_v<TRANSFORM>(a, box4<LEG>(vv, vb, vc, vd, false)));
+    store_plane3(a.nmap[2], a.pitch[2], a.rows[2], y2, x2, xform_n<TRANSFORM>(a, box4<LEG>(nn, nb, nc, nd, true)));
   }
 }
 
 cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4, const float4* n4, int pitch4,
-                                const float* pose16_or_null, float* zdepth, float zcut, cudaStream_t s) {
+                                const float* pose16_or_null, float* zdepth, float zcut, bool legacy, cudaStream_t s) {
   MapsPyrArgs a;
   a.v4 = v4; a.n4 = n4; a.pitch4 = pitch4; a.zdepth = zdepth; a.zcut = zcut;
   for (int i = 0; i < 3; ++i) {
@@ -120,10 +121,10 @@ cudaError_t launch_maps_pyramid(const Level* lv, bool use_prev, const float4* v4
     const float* p = pose16_or_null;
     a.R.r[0] = make_float3(p[0], p[1], p[2]); a.R.r[1] = make_float3(p[4], p[5], p[6]); a.R.r[2] = make_float3(p[8], p[9], p[10]);
     a.t = make_float3(p[3], p[7], p[11]);
-    k_maps_pyramid<true><<<grid, block, 0, s>>>(a);
+    if (legacy) k_maps_pyramid<true, true><<<grid, block, 0, s>>>(a); else k_maps_pyramid<true, false><<<grid, block, 0, s>>>(a);
   } else {
     a.R.r[0] = a.R.r[1] = a.R.r[2] = make_float3(0, 0, 0); a.t = make_float3(0, 0, 0);
-    k_maps_pyramid<false><<<grid, block, 0, s>>>(a);
+    if (legacy) k_maps_pyramid<false, true><<<grid, block, 0, s>>>(a); else k_maps_pyramid<false, false><<<grid, block, 0, s>>>(a);
   }
   return cudaGetLastError();
 }
@@ -180,7 +181,7 @@ __device__ __forceinline__ void gauss_tap_window(const float* sd, const unsigned
   *sumd_o = sumd; *cntd_o = cntd; *sumi_o = sumi; *cnti_o = cnti;
 }
 
-template <bool HAS_DEPTH>
+template <bool HAS_DEPTH, bool LEG>
 __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
   __shared__ float sd0[41][41];
   __shared__ unsigned char si0[41][44];
@@ -212,10 +213,10 @@ __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
     float sumd, sumi; int cntd, cnti;
     if (tx - cx0 == 5 && ty - cy0 == 5) gauss_tap_window<HAS_DEPTH, true, 41, 44>(&sd0[0][0], &si0[0][0], cx0 - ox0, cy0 - oy0, 5, 5, &sumd, &cntd, &sumi, &cnti);
     else gauss_tap_window<HAS_DEPTH, false, 41, 44>(&sd0[0][0], &si0[0][0], cx0 - ox0, cy0 - oy0, tx - cx0, ty - cy0, &sumd, &cntd, &sumi, &cnti);
-    const unsigned char iv1 = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));  // 0/0 -> NaN -> 0
+    const unsigned char iv1 = (unsigned char)__float2int_rz(div_t<LEG>(sumi, (float)cnti));  // 0/0 -> NaN -> 0
     si1[ly][lx] = iv1;
     float d1 = 0.f;
-    if (HAS_DEPTH) { d1 = fdiv(sumd, (float)cntd); sd1[ly][lx] = d1; }
+    if (HAS_DEPTH) { d1 = div_t<LEG>(sumd, (float)cntd); sd1[ly][lx] = d1; }
     if (lx >= 2 && lx < 18 && ly >= 2 && ly < 18) {
       row_ptr(a.img[1], a.pitch_i[1], y)[x] = iv1;
       if (HAS_DEPTH) row_ptr(a.depth[1], a.pitch_f[1], y)[x] = d1;
@@ -231,13 +232,13 @@ __global__ void __launch_bounds__(256) k_populate(const PopArgs a) {
       float sumd, sumi; int cntd, cnti;
       if (tx - cx0 == 5 && ty - cy0 == 5) gauss_tap_window<HAS_DEPTH, true, 19, 20>(&sd1[0][0], &si1[0][0], cx0 - ox1, cy0 - oy1, 5, 5, &sumd, &cntd, &sumi, &cnti);
       else gauss_tap_window<HAS_DEPTH, false, 19, 20>(&sd1[0][0], &si1[0][0], cx0 - ox1, cy0 - oy1, tx - cx0, ty - cy0, &sumd, &cntd, &sumi, &cnti);
-      row_ptr(a.img[2], a.pitch_i[2], y)[x] = (unsigned char)__float2int_rz(fdiv(sumi, (float)cnti));
-      if (HAS_DEPTH) row_ptr(a.depth[2], a.pitch_f[2], y)[x] = fdiv(sumd, (float)cntd);
+      row_ptr(a.img[2], a.pitch_i[2], y)[x] = (unsigned char)__float2int_rz(div_t<LEG>(sumi, (float)cnti));
+      if (HAS_DEPTH) row_ptr(a.depth[2], a.pitch_f[2], y)[x] = div_t<LEG>(sumd, (float)cntd);
     }
   }
 }
 
-cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, cudaStream_t s) {
+cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const uchar4* rgba, int pitch_rgba, bool legacy, cudaStream_t s) {
   // which: 0 = last (initRGBModel), 1 = next (initRGB), 2 = lastNext image only (initFirstRGB)
   PopArgs a;
   a.zsrc = zsrc; a.pitch_z = lv[0].pitch_f32; a.rgba = rgba; a.pitch_rgba = pitch_rgba;
@@ -247,8 +248,8 @@ cudaError_t launch_populate(const Level* lv, int which, const float* zsrc, const
     a.pitch_f[i] = lv[i].pitch_f32; a.pitch_i[i] = lv[i].pitch_u8; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols;
   }
   const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 31) / 32);
-  if (which == 2) k_populate<false><<<grid, 256, 0, s>>>(a);
-  else k_populate<true><<<grid, 256, 0, s>>>(a);
+  if (which == 2) { if (legacy) k_populate<false, true><<<grid, 256, 0, s>>>(a); else k_populate<false, false><<<grid, 256, 0, s>>>(a); }
+  else { if (legacy) k_populate<true, true><<<grid, 256, 0, s>>>(a); else k_populate<true, false><<<grid, 256, 0, s>>>(a); }
   return cudaGetLastError();
 }
 
@@ -263,6 +264,7 @@ struct IcpDepthArgs {
   Intr k[3]; float cutoff;
 };
 
+template <bool LEG>
 __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* tile, int tstride, int ox, int oy, int x, int y, int srows, int scols) {
   const int center = tile[(2 * y - oy) * tstride + (2 * x - ox)];
   const int x_mi = max(0, 2 * x - 2) - 2 * x, y_mi = max(0, 2 * y - 2) - 2 * y;
@@ -282,7 +284,7 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
         }
       }
     }
-    return (unsigned short)__float2int_rz(fdiv(sum, wall));
+    return (unsigned short)__float2int_rz(div_t<LEG>(sum, wall));
   }
   for (int yi = y_mi; yi < y_ma; ++yi) {
     const float wy = (yi == 0) ? 0.375f : (abs(yi) == 1 ? 0.25f : 0.0625f);
@@ -295,34 +297,37 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
       }
     }
   }
-  return (unsigned short)__float2int_rz(fdiv(sum, wall));
+  return (unsigned short)__float2int_rz(div_t<LEG>(sum, wall));
 }
 
+template <bool LEG>
 __device__ __forceinline__ float3 backproject_d(int d, int u, int v, const Intr& k, float fxi, float fyi, float cutoff) {
-  const float z = fdiv((float)d, 1000.f);
+  const float z = LEG ? fmul((float)d, 0.001f) : fdiv((float)d, 1000.f);  // cf.cu:116: nvcc folds the division by a constant under --prec-div=false
   if (z != 0 && z < cutoff) return make_float3(fmul(fmul(z, fsub((float)u, k.cx)), fxi), fmul(fmul(z, fsub((float)v, k.cy)), fyi), z);
   return make_float3(qnan(), qnan(), qnan());
 }
 
 // vertex + normal of the own block of one level from its shared depth tile
+template <bool LEG>
 __device__ __forceinline__ void vn_block(const unsigned short* tile, int tstride, int ox, int oy, int bx0, int by0, int bw, int rows, int cols,
                                          const Intr& k, float cutoff, float* vmap, float* nmap, int pitch) {
   const float fxi = fdiv(1.f, k.fx), fyi = fdiv(1.f, k.fy);
   for (int idx = threadIdx.x; idx < bw * bw; idx += blockDim.x) {
     const int ly = idx / bw, lx = idx - ly * bw, u = bx0 + lx, v = by0 + ly;
     if (u >= cols || v >= rows) continue;
-    const float3 v00 = backproject_d(tile[(v - oy) * tstride + (u - ox)], u, v, k, fxi, fyi, cutoff);
+    const float3 v00 = backproject_d<LEG>(tile[(v - oy) * tstride + (u - ox)], u, v, k, fxi, fyi, cutoff);
     store_plane3(vmap, pitch, rows, v, u, v00);
     float3 n = make_float3(qnan(), qnan(), qnan());
     if (u < cols - 1 && v < rows - 1) {
-      const float3 v01 = backproject_d(tile[(v - oy) * tstride + (u + 1 - ox)], u + 1, v, k, fxi, fyi, cutoff);
-      const float3 v10 = backproject_d(tile[(v + 1 - oy) * tstride + (u - ox)], u, v + 1, k, fxi, fyi, cutoff);
-      if (!isnan(v00.x) && !isnan(v01.x) && !isnan(v10.x)) n = normalized3(cross3(sub3(v01, v00), sub3(v10, v00)));
+      const float3 v01 = backproject_d<LEG>(tile[(v - oy) * tstride + (u + 1 - ox)], u + 1, v, k, fxi, fyi, cutoff);
+      const float3 v10 = backproject_d<LEG>(tile[(v + 1 - oy) * tstride + (u - ox)], u, v + 1, k, fxi, fyi, cutoff);
+      if (!isnan(v00.x) && !isnan(v01.x) && !isnan(v10.x)) n = normalized3_t<LEG>(cross3(sub3(v01, v00), sub3(v10, v00)));
     }
     store_plane3(nmap, pitch, rows, v, u, n);
   }
 }
 
+template <bool LEG>
 __global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
   __shared__ unsigned short t0[45 * 46];
   __shared__ unsigned short t1[21 * 22];
@@ -340,7 +345,7 @@ __global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
   for (int idx = tid; idx < 21 * 21; idx += 256) {
     const int ly = idx / 21, lx = idx - ly * 21, x = ox1 + lx, y = oy1 + ly;
     if (x < 0 || y < 0 || x >= a.cols[1] || y >= a.rows[1]) continue;
-    const unsigned short d = pyrdown_u16_tap(t0, 46, ox0, oy0, x, y, a.rows[0], a.cols[0]);
+    const unsigned short d = pyrdown_u16_tap<LEG>(t0, 46, ox0, oy0, x, y, a.rows[0], a.cols[0]);
     t1[ly * 22 + lx] = d;
     if (lx >= 2 && lx < 18 && ly >= 2 && ly < 18) row_ptr(a.dt[1], a.pitch_u16[1], y)[x] = d;
   }
@@ -348,18 +353,18 @@ __global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
   if (tid < 81) {
     const int ly = tid / 9, lx = tid - ly * 9, x = ox2 + lx, y = oy2 + ly;
     if (x < a.cols[2] && y < a.rows[2]) {
-      const unsigned short d = pyrdown_u16_tap(t1, 22, ox1, oy1, x, y, a.rows[1], a.cols[1]);
+      const unsigned short d = pyrdown_u16_tap<LEG>(t1, 22, ox1, oy1, x, y, a.rows[1], a.cols[1]);
       t2[ly * 10 + lx] = d;
       if (lx < 8 && ly < 8) row_ptr(a.dt[2], a.pitch_u16[2], y)[x] = d;
     }
   }
   __syncthreads();
-  vn_block(t0, 46, ox0, oy0, 32 * bx, 32 * by, 32, a.rows[0], a.cols[0], a.k[0], a.cutoff, a.vmap[0], a.nmap[0], a.pitch_f[0]);
-  vn_block(t1, 22, ox1, oy1, 16 * bx, 16 * by, 16, a.rows[1], a.cols[1], a.k[1], a.cutoff, a.vmap[1], a.nmap[1], a.pitch_f[1]);
-  vn_block(t2, 10, ox2, oy2, 8 * bx, 8 * by, 8, a.rows[2], a.cols[2], a.k[2], a.cutoff, a.vmap[2], a.nmap[2], a.pitch_f[2]);
+  vn_block<LEG>(t0, 46, ox0, oy0, 32 * bx, 32 * by, 32, a.rows[0], a.cols[0], a.k[0], a.cutoff, a.vmap[0], a.nmap[0], a.pitch_f[0]);
+  vn_block<LEG>(t1, 22, ox1, oy1, 16 * bx, 16 * by, 16, a.rows[1], a.cols[1], a.k[1], a.cutoff, a.vmap[1], a.nmap[1], a.pitch_f[1]);
+  vn_block<LEG>(t2, 10, ox2, oy2, 8 * bx, 8 * by, 8, a.rows[2], a.cols[2], a.k[2], a.cutoff, a.vmap[2], a.nmap[2], a.pitch_f[2]);
 }
 
-cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, cudaStream_t s) {
+cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, bool legacy, cudaStream_t s) {
   IcpDepthArgs a;
   a.depth = d_depth; a.pitch_in = pitch_in; a.cutoff = cutoff;
   for (int i = 0; i < 3; ++i) {
@@ -367,7 +372,7 @@ cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int
     a.pitch_u16[i] = lv[i].pitch_u16; a.pitch_f[i] = lv[i].pitch_f32; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols; a.k[i] = lv[i].intr;
   }
   const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 31) / 32);
-  k_icp_depth<<<grid, 256, 0, s>>>(a);
+  if (legacy) k_icp_depth<true><<<grid, 256, 0, s>>>(a); else k_icp_depth<false><<<grid, 256, 0, s>>>(a);
   return cudaGetLastError();
 }
 

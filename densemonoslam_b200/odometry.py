@@ -248,6 +248,10 @@ class RGBDOdometry:
         """0 spin (default), 1 blocking-sync event, 2 sleep for most of the expected wait then poll and yield."""
         self._ck(self._L.dms_odom_set_wait(self._h, int(mode)), "set_wait")
 
+    def set_numerics(self, mode):
+        """"ieee" (default, = the CPU oracle's arithmetic) or "legacy" (the reference build's approximate divisions / square roots)."""
+        self._ck(self._L.dms_odom_set_numerics(self._h, {"ieee": 0, "legacy": 1}[mode] if isinstance(mode, str) else int(mode)), "set_numerics")
+
     def set_timing(self, mode=1):
         """0 = off, 1 = kernel events + per-phase counters, 2 = additionally the timeline of timeline()."""
         self._ck(self._L.dms_odom_set_timing(self._h, int(mode)), "set_timing")

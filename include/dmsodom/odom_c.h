@@ -84,6 +84,18 @@ int dms_odom_set_block(dms_odom* h, int threads);
  * (many trackers / ranks per host core without the wake-up latency of 1), 3 = as 2 but polling with 20 us sleeps instead
  * of yields (more waiting threads than host cores). */
 int dms_odom_set_wait(dms_odom* h, int mode);
+/* Arithmetic of the divisions and square roots that feed a truncation, a pixel rounding or a threshold test.
+ * DMS_NUMERICS_IEEE (default): correctly rounded IEEE operations, the arithmetic the CPU oracle restates; integer outputs
+ *   then differ from the reference BUILD in a bounded handful of places (+-1 on < 1 % of the pyramid pixels, single
+ *   correspondences at a threshold), because that build approximates.
+ * DMS_NUMERICS_LEGACY: the instructions nvcc emits for the reference under its own flags --ftz=true --prec-div=false
+ *   --prec-sqrt=false (Core/src/CMakeLists.txt:48-49): div.full.ftz, rcp/sqrt/rsqrt.approx.ftz, x * 0.001f for x / 1000.f, at
+ *   cudafuncs.cu:86-90,116,169,440-442,570-572, operators.cuh:77-86 and reduce.cu:270-271,294-302,569-576,806-815,970-971.
+ *   Integer outputs (intensity and depth pyramids, derivative images, correspondence records, inlier counts) are then
+ *   identical to the reference's own kernels (tests/test_gpu_vs_legacy.py).  Applies to the init_* calls, the track and
+ *   the step operators issued after the switch. */
+enum dms_numerics { DMS_NUMERICS_IEEE = 0, DMS_NUMERICS_LEGACY = 1 };
+int dms_odom_set_numerics(dms_odom* h, int mode);
 /* mode 0 = off (default), 1 = CUDA events around the kernel + per-phase counters of thread block 0 (a few clock reads per
  * phase), 2 = additionally the {tag, timestamp} timeline read by dms_odom_get_timeline (a memset per track). */
 int dms_odom_set_timing(dms_odom* h, int mode);

@@ -110,6 +110,58 @@ def legacy_stages(ref, cam, c):
     return out
 
 
+def product_stages(g, torch, cam, c):
+    """The same stages through the PRODUCT path (C ABI of libdmsodom.so via the Python mirror `g`): pyramids downloaded
+    after the init_* calls, the four step operators for the reductions."""
+    from densemonoslam_b200.odometry import CORR_DTYPE  # noqa: F401
+    m, l = c["model"], c["live"]
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    out = {}
+    # model side: maps in the global frame, depth / image pyramids of the model view
+    g.initICPModel(dev(m["vmap4"]), dev(m["nmap4"]), 25.0, c["pose"])
+    g.initRGBModel(dev(m["rgba"]))
+    for i in range(3):
+        out[f"mv{i}"] = g.download("vmap_g_prev", i); out[f"mn{i}"] = g.download("nmap_g_prev", i)
+    out.update(zd=g.download("lastDepth", 0), zd1=g.download("lastDepth", 1))
+    # live side from the live vertex map (nextDepth = its z channel), derivative images, photometric stage
+    g.initICP(dev(l["vmap4"]), dev(l["nmap4"]), 25.0)
+    g.initRGB(dev(l["rgba"]))
+    out.update(I0=g.download("nextImage", 0), I1=g.download("nextImage", 1), I2=g.download("nextImage", 2))
+    g.computeDerivativeImages()
+    out.update(dx=g.download("dIdx", 0), dy=g.download("dIdy", 0))
+    cnt, sig = g.computeRgbResidual(0, c["kt"], c["krkinv"])
+    corr = g.download("corr", 0)
+    p2, _ = g.rgbStep(0, float(np.float32(np.sqrt(np.float32(cnt)))))
+    A2, b2 = unpack28(p2)
+    out.update(rgb_valid=corr["valid"].copy(), rgb_u0=corr["u0"].copy(), rgb_v0=corr["v0"].copy(), rgb_diff=corr["diff"].copy(),
+               rgb_count=np.int64(cnt), rgb_sigma=np.int64(sig), rgb_A=A2, rgb_b=b2)
+    # SO(3): model image (as previous frame) against the live image at level 2
+    g.initFirstRGB(dev(m["rgba"]))
+    p3, c3 = g.so3Step(2, c["so3_H"], c["so3_kinv"], c["so3_krlr"])
+    A3, b3 = unpack10(p3); out.update(so3_A=A3, so3_b=b3, so3_res=np.float32(p3[9]), so3_count=np.int64(c3))
+    # live side from the sensor depth: u16 pyramid, vertex / normal maps, ICP step
+    g.initICP(dev(l["depth"]), 25.0)
+    out.update(d1=g.download("depth_tmp", 1), d2=g.download("depth_tmp", 2), vmap=g.download("vmap_curr", 0), nmap=g.download("nmap_curr", 0))
+    p, inl = g.icpStep(0, c["Rc"], c["tc"], c["Rprev_inv"], c["tprev"])
+    A, b = unpack28(p); out.update(icp_A=A, icp_b=b, icp_res=np.float32(p[27]), icp_inliers=np.int64(inl))
+    return out
+
+
+def check_identical_integers(rep):
+    """Product path in legacy-numerics mode vs the reference's kernels: every integer output identical, counts identical,
+    the float outputs within the stated tolerance (the summation order of the reduced systems differs)."""
+    for k in INT_KEYS:
+        assert rep[k]["mismatch"] == 0, (k, rep[k])
+    for k in COUNT_KEYS:
+        assert rep[k]["oracle"] == rep[k]["reference"], (k, rep[k])
+    for k in MAP_KEYS:
+        assert rep[k]["nan_pattern_mismatch"] == 0, (k, rep[k])
+    for k in F32_KEYS:
+        assert rep[k]["nan_pattern_mismatch"] == 0, (k, rep[k])
+    for k in SYS_KEYS:
+        assert rep[k]["max_rel_to_norm"] <= 1e-4, (k, rep[k])
+
+
 INT_KEYS = ["I0", "I1", "I2", "d1", "d2", "dx", "dy", "rgb_valid", "rgb_u0", "rgb_v0", "rgb_diff"]
 MAP_KEYS = ["vmap", "nmap", "mv0", "mn0", "mv1", "mn1", "mv2", "mn2"]
 F32_KEYS = ["zd", "zd1"]
