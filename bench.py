@@ -210,7 +210,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=8, help="trackers sharing the GPU concurrently (1 = strictly sequential frames)")
+    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 8, fewer for short runs so that every tracker gets several frames)")
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 768)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -222,7 +222,7 @@ def main():
 
     if args.wait < 0:
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
-        args.wait = 3 if local_world * max(1, args.pipeline) > len(os.sched_getaffinity(0)) else 2
+        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else 8) > len(os.sched_getaffinity(0)) else 2
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -360,6 +360,16 @@ def main():
             t = torch.tensor([ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
+        # host-side timeline of the timed call (per rank; max and median over ranks): where a short region spends its time
+        tl = torch.tensor(seq.host_timeline(), device="cuda", dtype=torch.float64)
+        if world > 1:
+            allv = [torch.zeros_like(tl) for _ in range(world)]
+            dist.all_gather(allv, tl)
+            allv = torch.stack(allv).cpu().numpy()
+        else:
+            allv = tl.cpu().numpy()[None]
+        timed_native.host_timeline = {"unit": "us since the entry of dms_sequence_run", "keys": ["first_k_track_enqueued", "last_result_collected", "returned"],
+                                      "max_over_ranks": [float(v) for v in allv.max(0)], "median_over_ranks": [float(v) for v in np.median(allv, 0)]}
         ktimes = [r.track_ms for r in res]
         iters_seen = [list(r.r.iters) for r in res]
         so3_seen = [r.r.so3_iters for r in res]
@@ -439,7 +449,10 @@ def main():
                 "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
-    depth = max(1, args.pipeline)
+    # trackers sharing the GPU: 8 in a long run; a short run (the driver's 20 steps) fills and drains the pipeline once, which
+    # costs less with fewer, larger trackers (measured: tools/quick_perf.py)
+    depth = max(1, args.pipeline) if args.pipeline else min(8, max(2, args.steps // 3))
+    depth_e2e = max(1, args.pipeline) if args.pipeline else min(6, max(2, args.steps // 5))   # uploads inside the region: PCIe-bound, fewer trackers start sooner
     _thr = args.threads if args.threads else 768
     _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, 8)
     config_exec["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
@@ -459,15 +472,27 @@ def main():
         pipe = make_pipe(depth)
         ms, ktimes, iters_seen, so3_seen, clocks, last = timed(pipe, args.steps, args.warmup, False)
     value = world * args.steps / (ms * 1e-3)
+    if native:
+        config_exec["host_timeline"] = timed_native.host_timeline
     gt = frames[(args.steps - 1) % ring]["gt"]
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
     roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, 8) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
 
     if args.quick:
-        emit({"value": value, "roofline": roofline, "config": config, "config_exec": config_exec, "clocks": clocks})
+        if rank == 0:
+            emit({"value": value, "roofline": roofline, "config": config, "config_exec": config_exec, "clocks": clocks})
         return
     e2e_steps = min(args.steps, 300)
-    ms_e2e, _, _, _, _, last_e2e = timed_native(seq, e2e_steps, min(args.warmup, 5), True) if native else timed(pipe, e2e_steps, min(args.warmup, 5), True)
+    if native:
+        if depth_e2e != depth:
+            del seq
+            seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth_e2e, block_threads=args.threads,
+                                  grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
+                                  fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
+        config_exec["pipeline_e2e"] = f"{depth_e2e} trackers, each with two input stages on the device and a copy stream (frame f + {depth_e2e} uploads under frame f's kernels)"
+        ms_e2e, _, _, _, _, last_e2e = timed_native(seq, e2e_steps, min(args.warmup, 5), True)
+    else:
+        ms_e2e, _, _, _, _, last_e2e = timed(pipe, e2e_steps, min(args.warmup, 5), True)
     pose_err_e2e = float(np.max(np.abs(last_e2e[0] - frames[(e2e_steps - 1) % ring]["gt"][:3, 3])))
     e2e_value = world * e2e_steps / (ms_e2e * 1e-3)
 

@@ -148,6 +148,7 @@ SIGNATURES = {
     "dms_sequence_destroy": (C.c_int, [_P]),
     "dms_sequence_run": (C.c_int, [_P, C.POINTER(DmsSeqFrame), C.c_int, _P, C.c_int, C.POINTER(DmsSeqResult)]),
     "dms_sequence_resident": (C.c_int, [_P]),
+    "dms_sequence_host_timeline": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

@@ -109,7 +109,8 @@ static void mat3_inv_t(const double* m, double* o) {  // o = inverse(m) transpos
   o[3] = (m[2] * m[7] - m[1] * m[8]) * id; o[4] = (m[0] * m[8] - m[2] * m[6]) * id; o[5] = (m[1] * m[6] - m[0] * m[7]) * id;
   o[6] = (m[1] * m[5] - m[2] * m[4]) * id; o[7] = (m[2] * m[3] - m[0] * m[5]) * id; o[8] = (m[0] * m[4] - m[1] * m[3]) * id;
 }
-// ElasticFusion::rodrigues2 (EF.cpp:941-986).  R = U * V^T of the SVD is the orthogonal polar factor, obtained
+// ElasticFusion::rodrigues2 (elasticfusion/Core/src/ElasticFusion.cpp:941-986), restated without Eigen / OpenCV: the host
+// math of the reference's gate, kept in its operation order on purpose (parity of the loop-closure gate needs it).  R = U * V^T of the SVD is the orthogonal polar factor, obtained
 // here by Newton's iteration X <- (X + X^-T) / 2 (quadratic convergence from a near-rotation).
 static void rodrigues2(const float* Rf, double out[3]) {
   double R[9], T[9];
@@ -376,9 +377,18 @@ int dms_frontend_process(dms_frontend* fe, const uint8_t* d_rgba, size_t rgba_pi
           fe->lastFrameRecovery = 0;
         }
       }
-      fe->currPose[3] = trans[0]; fe->currPose[7] = trans[1]; fe->currPose[11] = trans[2];
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) fe->currPose[i * 4 + j] = rot[i * 3 + j];
+      // a non-finite pose (a partial sum overflowed the accumulators, or a NaN came in with the inputs) must not become the
+      // state the next frame starts from: keep the pose the frame started with and report the frame as not tracked
+      bool finite = true;
+      for (int i = 0; i < 3; ++i) finite = finite && isfinite(trans[i]);
+      for (int i = 0; i < 9; ++i) finite = finite && isfinite(rot[i]);
+      if (finite) {
+        fe->currPose[3] = trans[0]; fe->currPose[7] = trans[1]; fe->currPose[11] = trans[2];
+        for (int i = 0; i < 3; ++i)
+          for (int j = 0; j < 3; ++j) fe->currPose[i * 4 + j] = rot[i * 3 + j];
+      } else {
+        trackingOk = 0;
+      }
     }
     out->trackingOk = trackingOk;
     out->weighting = dms_velocity_weighting(fe->currPose, lastPose, o.weightMultiplier);  // EF.cpp:251-266

@@ -42,6 +42,12 @@ class SequenceTracker:
     def resident(self):
         return int(self._L.dms_sequence_resident(self._h))
 
+    def host_timeline(self):
+        """(first tracking kernel enqueued, last result collected, return) of the last run, microseconds since its entry"""
+        us = (C.c_double * 3)()
+        self._L.dms_sequence_host_timeline(self._h, us)
+        return [float(v) for v in us]
+
     def make_frames(self, frames):
         """frames: list of dicts {"v", "n", "mi", "d", "li": tensors / arrays, "prior": 4x4}; returns the C array (keeps references)."""
         arr = (_lib.DmsSeqFrame * len(frames))()

@@ -51,6 +51,9 @@ int dms_sequence_destroy(dms_sequence* s);
  * Blocks until all results are in `out`.  Returns 0 or the first error. */
 int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n_frames, const uint8_t* first_prev_rgba,
                      int host_buffers, dms_seq_result* out);
+/* Host-side timeline of the last dms_sequence_run, microseconds since its entry: [0] the first tracking kernel was
+ * enqueued, [1] the last result was collected, [2] the call returned.  Diagnostic for short runs and many ranks per host. */
+int dms_sequence_host_timeline(const dms_sequence* s, double us[3]);
 /* resident tracking kernels = min(n_trackers, block slots / grid) */
 int dms_sequence_resident(const dms_sequence* s);
 

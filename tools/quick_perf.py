@@ -33,6 +33,11 @@ dev = [{"v": torch.from_numpy(f["model"]["vmap4"]).cuda(), "n": torch.from_numpy
         "d": torch.from_numpy(f["live"]["depth"]).cuda(), "li": torch.from_numpy(f["live"]["rgba"]).cuda(), "prior": f["prior"]} for f in frames]
 
 
+HOST = os.environ.get("QP_HOST", "0") == "1"   # end-to-end shape: pinned host inputs, uploads inside the timed region
+if HOST:
+    dev = [{k: (v.cpu().pin_memory() if hasattr(v, "cpu") else v) for k, v in d.items()} for d in dev]
+
+
 def frame_list(n):
     return [dev[i % ring] for i in range(n)]
 
@@ -44,16 +49,16 @@ for cfg in cfgs:
     seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, n_trackers=trackers, block_threads=threads if trackers > 1 or threads != 1024 else 0,
                           grid=grid, wait_mode=2 if trackers > 1 else 0, timing=1)
     first_prev = dev[-1]["li"]
-    seq.run(seq.make_frames(frame_list(3 * trackers)), first_prev, False)
+    seq.run(seq.make_frames(frame_list(3 * trackers)), first_prev, HOST)
     fc = seq.make_frames(frame_list(steps))
     torch.cuda.synchronize()
     best = None
     for rep in range(3):
         t0 = time.perf_counter()
-        res = seq.run(fc, first_prev, False)
+        res = seq.run(fc, first_prev, HOST)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         best = dt if best is None or dt < best else best
     k_ms = float(np.mean([r.track_ms for r in res]))
-    print(f"{name} {cfg:>12s}: {steps / best:8.0f} frames/s  k_track {k_ms * 1000:7.1f} us  resident {seq.resident}", flush=True)
+    print(f"{name} {"host" if HOST else "dev"} {cfg:>12s}: {steps / best:8.0f} frames/s  k_track {k_ms * 1000:7.1f} us  resident {seq.resident}", flush=True)
     del seq
