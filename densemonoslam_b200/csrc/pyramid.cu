@@ -261,7 +261,8 @@ struct IcpDepthArgs {
   const unsigned short* depth; int pitch_in;
   unsigned short* dt[3]; float* vmap[3]; float* nmap[3];
   int pitch_u16[3], pitch_f[3], rows[3], cols[3];
-  Intr k[3]; float cutoff;
+  Intr k[3]; float fxi[3], fyi[3];  // 1.f / fx, 1.f / fy as the reference's host code passes them (cf.cu:136-137)
+  float cutoff;
 };
 
 template <bool LEG>
@@ -277,7 +278,7 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
 #pragma unroll
       for (int xi = -2; xi <= 2; ++xi) {
         const int val = tile[(2 * y + yi - oy) * tstride + (2 * x + xi - ox)];
-        if ((float)abs(val - center) < 90.0f) {
+        if (abs(val - center) < 90) {  // cf.cu:79 compares (float)abs(.) < 90.0f: the same test on integers below 2^24
           const float wx = (xi == 0) ? 0.375f : ((xi == 1 || xi == -1) ? 0.25f : 0.0625f);
           sum = ffma(fmul((float)val, wx), wy, sum);
           wall = ffma(wx, wy, wall);
@@ -290,7 +291,7 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
     const float wy = (yi == 0) ? 0.375f : (abs(yi) == 1 ? 0.25f : 0.0625f);
     for (int xi = x_mi; xi < x_ma; ++xi) {
       const int val = tile[(2 * y + yi - oy) * tstride + (2 * x + xi - ox)];
-      if ((float)abs(val - center) < 90.0f) {
+      if (abs(val - center) < 90) {  // cf.cu:79 compares (float)abs(.) < 90.0f: the same test on integers below 2^24
         const float wx = (xi == 0) ? 0.375f : (abs(xi) == 1 ? 0.25f : 0.0625f);
         sum = ffma(fmul((float)val, wx), wy, sum);
         wall = ffma(wx, wy, wall);
@@ -300,9 +301,16 @@ __device__ __forceinline__ unsigned short pyrdown_u16_tap(const unsigned short* 
   return (unsigned short)__float2int_rz(div_t<LEG>(sum, wall));
 }
 
+// d / 1000.f, correctly rounded, for an integer d in [0, 65535]: product with RN(1/1000), exact remainder, one correction
+// (Markstein's scheme; checked against the IEEE quotient for all 65536 inputs) - 3 instructions instead of
+// the ~10 of a general IEEE division.
+__device__ __forceinline__ float mm_to_m(float d) {
+  const float q = fmul(d, 0.001f);
+  return ffma(ffma(-q, 1000.f, d), 0.001f, q);
+}
 template <bool LEG>
 __device__ __forceinline__ float3 backproject_d(int d, int u, int v, const Intr& k, float fxi, float fyi, float cutoff) {
-  const float z = LEG ? fmul((float)d, 0.001f) : fdiv((float)d, 1000.f);  // cf.cu:116: nvcc folds the division by a constant under --prec-div=false
+  const float z = LEG ? fmul((float)d, 0.001f) : mm_to_m((float)d);  // cf.cu:116; LEG: nvcc folds the division by a constant under --prec-div=false
   if (z != 0 && z < cutoff) return make_float3(fmul(fmul(z, fsub((float)u, k.cx)), fxi), fmul(fmul(z, fsub((float)v, k.cy)), fyi), z);
   return make_float3(qnan(), qnan(), qnan());
 }
@@ -310,8 +318,7 @@ __device__ __forceinline__ float3 backproject_d(int d, int u, int v, const Intr&
 // vertex + normal of the own block of one level from its shared depth tile
 template <bool LEG>
 __device__ __forceinline__ void vn_block(const unsigned short* tile, int tstride, int ox, int oy, int bx0, int by0, int bw, int rows, int cols,
-                                         const Intr& k, float cutoff, float* vmap, float* nmap, int pitch) {
-  const float fxi = fdiv(1.f, k.fx), fyi = fdiv(1.f, k.fy);
+                                         const Intr& k, float fxi, float fyi, float cutoff, float* vmap, float* nmap, int pitch) {
   for (int idx = threadIdx.x; idx < bw * bw; idx += blockDim.x) {
     const int ly = idx / bw, lx = idx - ly * bw, u = bx0 + lx, v = by0 + ly;
     if (u >= cols || v >= rows) continue;
@@ -327,19 +334,61 @@ __device__ __forceinline__ void vn_block(const unsigned short* tile, int tstride
   }
 }
 
+// Level 0 (three quarters of the pixels) needs no pyramid and no tile: a warp owns a strip of 31 columns x 4 rows, every lane
+// back-projects the 5 depths of its column once (1.25 per pixel instead of 3), takes the right neighbour's vertex from the
+// next lane (lane 31 only supplies it) and the lower neighbour's from its own next row.
+static const int L0_RUN = 4;
 template <bool LEG>
-__global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
-  __shared__ unsigned short t0[45 * 46];
+__device__ __forceinline__ void icp_depth_level0(const IcpDepthArgs& a, int strip) {
+  const int lane = threadIdx.x & 31, rows = a.rows[0], cols = a.cols[0];
+  const int wpr = (cols + 30) / 31;
+  const int sy = strip / wpr, sx = strip - sy * wpr;
+  const int x = sx * 31 + lane, y0 = sy * L0_RUN;
+  if (y0 >= rows) return;
+  const Intr k = a.k[0];
+  const float fxi = a.fxi[0], fyi = a.fyi[0];
+  float3 v[L0_RUN + 1];
+#pragma unroll
+  for (int r = 0; r <= L0_RUN; ++r) {
+    const int y = y0 + r;
+    const bool in = x < cols && y < rows;
+    const unsigned short d = in ? __ldg(row_ptr(a.depth, a.pitch_in, y) + x) : (unsigned short)0;
+    if (r < L0_RUN && lane < 31 && in) row_ptr(a.dt[0], a.pitch_u16[0], y)[x] = d;
+    v[r] = backproject_d<LEG>(d, x, y, k, fxi, fyi, a.cutoff);
+  }
+#pragma unroll
+  for (int r = 0; r < L0_RUN; ++r) {
+    const int y = y0 + r;
+    const float3 v00 = v[r], v10 = v[r + 1];
+    const float3 v01 = make_float3(__shfl_down_sync(0xffffffffu, v00.x, 1), __shfl_down_sync(0xffffffffu, v00.y, 1), __shfl_down_sync(0xffffffffu, v00.z, 1));
+    if (lane == 31 || x >= cols || y >= rows) continue;
+    store_plane3(a.vmap[0], a.pitch_f[0], rows, y, x, v00);
+    float3 n = make_float3(qnan(), qnan(), qnan());
+    if (x < cols - 1 && y < rows - 1 && !isnan(v00.x) && !isnan(v01.x) && !isnan(v10.x)) n = normalized3_t<LEG>(cross3(sub3(v01, v00), sub3(v10, v00)));
+    store_plane3(a.nmap[0], a.pitch_f[0], rows, y, x, n);
+  }
+}
+
+// One launch, two kinds of thread blocks: blocks [0, n_l0) run icp_depth_level0 (8 strips each); the others own a 32x32
+// level-0 block each and build the two coarser levels from shared-memory tiles of the u16 depth (45x45 / 21x21 / 9x9, one
+// extra row / column for the forward differences of the normals), the tile fetched as 32-bit pairs.
+template <bool LEG>
+__global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a, int n_l0, int tiles_x) {
+  if ((int)blockIdx.x < n_l0) { icp_depth_level0<LEG>(a, blockIdx.x * 8 + (threadIdx.x >> 5)); return; }
+  __shared__ __align__(4) unsigned short t0[45 * 46];
   __shared__ unsigned short t1[21 * 22];
   __shared__ unsigned short t2[9 * 10];
-  const int tid = threadIdx.x, bx = blockIdx.x, by = blockIdx.y;
+  const int tid = threadIdx.x, tile = blockIdx.x - n_l0, by = tile / tiles_x, bx = tile - by * tiles_x;
   const int ox0 = 32 * bx - 6, oy0 = 32 * by - 6, ox1 = 16 * bx - 2, oy1 = 16 * by - 2, ox2 = 8 * bx, oy2 = 8 * by;
-  for (int idx = tid; idx < 45 * 45; idx += 256) {
-    const int ly = idx / 45, lx = idx - ly * 45, gx = ox0 + lx, gy = oy0 + ly;
-    if (gx < 0 || gy < 0 || gx >= a.cols[0] || gy >= a.rows[0]) continue;
-    const unsigned short d = __ldg(row_ptr(a.depth, a.pitch_in, gy) + gx);
-    t0[ly * 46 + lx] = d;
-    if (lx >= 6 && lx < 38 && ly >= 6 && ly < 38) row_ptr(a.dt[0], a.pitch_u16[0], gy)[gx] = d;
+  // rows of 46 = 23 pairs; ox0 is even and rows are 256-byte aligned, so a pair never straddles an alignment boundary
+  for (int idx = tid; idx < 45 * 23; idx += 256) {
+    const int ly = idx / 23, lp = idx - ly * 23, gx = ox0 + 2 * lp, gy = oy0 + ly;
+    unsigned int w = 0u;
+    if (gy >= 0 && gy < a.rows[0] && gx >= 0 && gx < a.cols[0]) {
+      if (gx + 1 < a.cols[0] && (a.pitch_in & 3) == 0 && ((size_t)a.depth & 3) == 0) w = __ldg(reinterpret_cast<const unsigned int*>(row_ptr(a.depth, a.pitch_in, gy) + gx));
+      else w = (unsigned int)__ldg(row_ptr(a.depth, a.pitch_in, gy) + gx) | (gx + 1 < a.cols[0] ? (unsigned int)__ldg(row_ptr(a.depth, a.pitch_in, gy) + gx + 1) << 16 : 0u);
+    }
+    *reinterpret_cast<unsigned int*>(&t0[ly * 46 + 2 * lp]) = w;
   }
   __syncthreads();
   for (int idx = tid; idx < 21 * 21; idx += 256) {
@@ -359,9 +408,8 @@ __global__ void __launch_bounds__(256) k_icp_depth(const IcpDepthArgs a) {
     }
   }
   __syncthreads();
-  vn_block<LEG>(t0, 46, ox0, oy0, 32 * bx, 32 * by, 32, a.rows[0], a.cols[0], a.k[0], a.cutoff, a.vmap[0], a.nmap[0], a.pitch_f[0]);
-  vn_block<LEG>(t1, 22, ox1, oy1, 16 * bx, 16 * by, 16, a.rows[1], a.cols[1], a.k[1], a.cutoff, a.vmap[1], a.nmap[1], a.pitch_f[1]);
-  vn_block<LEG>(t2, 10, ox2, oy2, 8 * bx, 8 * by, 8, a.rows[2], a.cols[2], a.k[2], a.cutoff, a.vmap[2], a.nmap[2], a.pitch_f[2]);
+  vn_block<LEG>(t1, 22, ox1, oy1, 16 * bx, 16 * by, 16, a.rows[1], a.cols[1], a.k[1], a.fxi[1], a.fyi[1], a.cutoff, a.vmap[1], a.nmap[1], a.pitch_f[1]);
+  vn_block<LEG>(t2, 10, ox2, oy2, 8 * bx, 8 * by, 8, a.rows[2], a.cols[2], a.k[2], a.fxi[2], a.fyi[2], a.cutoff, a.vmap[2], a.nmap[2], a.pitch_f[2]);
 }
 
 cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int pitch_in, float cutoff, bool legacy, cudaStream_t s) {
@@ -370,9 +418,12 @@ cudaError_t launch_icp_depth(const Level* lv, const unsigned short* d_depth, int
   for (int i = 0; i < 3; ++i) {
     a.dt[i] = lv[i].depth_tmp; a.vmap[i] = lv[i].vmap_curr; a.nmap[i] = lv[i].nmap_curr;
     a.pitch_u16[i] = lv[i].pitch_u16; a.pitch_f[i] = lv[i].pitch_f32; a.rows[i] = lv[i].rows; a.cols[i] = lv[i].cols; a.k[i] = lv[i].intr;
+    a.fxi[i] = 1.f / lv[i].intr.fx; a.fyi[i] = 1.f / lv[i].intr.fy;
   }
-  const dim3 grid((lv[0].cols + 31) / 32, (lv[0].rows + 31) / 32);
-  if (legacy) k_icp_depth<true><<<grid, 256, 0, s>>>(a); else k_icp_depth<false><<<grid, 256, 0, s>>>(a);
+  const int strips = ((lv[0].cols + 30) / 31) * ((lv[0].rows + L0_RUN - 1) / L0_RUN);
+  const int n_l0 = (strips + 7) / 8, tiles_x = (lv[0].cols + 31) / 32, tiles_y = (lv[0].rows + 31) / 32;
+  const int grid = n_l0 + tiles_x * tiles_y;
+  if (legacy) k_icp_depth<true><<<grid, 256, 0, s>>>(a, n_l0, tiles_x); else k_icp_depth<false><<<grid, 256, 0, s>>>(a, n_l0, tiles_x);
   return cudaGetLastError();
 }
 
