@@ -345,6 +345,10 @@ def main():
         first_prev = src[(0 - 1) % ring]["li"]
         seq.run(seq.make_frames(frame_list(max(3, warmup) * max(1, seq.options.n_trackers))), first_prev, host)
         fc = seq.make_frames(frame_list(steps))
+        rring = getattr(seq, "_ring", None)
+        if rring is not None and rring.owner:
+            torch.cuda.synchronize()
+            rring.clear()    # the warm-up frames carry the same frame numbers; producers are idle until the barrier below
         barrier()
         sampler = ClockSampler(local_rank)
         sampler.start()
@@ -352,6 +356,18 @@ def main():
         ev0.record()
         res = seq.run(fc, first_prev, host)
         torch.cuda.synchronize()
+        if rring is not None and rring.owner:
+            # the consumer of the multi-sensor mode: every sensor's per-frame record must have arrived in this GPU's memory
+            # (written there by the producing GPU behind each tracking kernel); part of the timed region
+            n_chk = min(steps, rring.slots)
+            t_end = time.perf_counter() + 10.0
+            got = [0] * rring.n_sensors
+            while time.perf_counter() < t_end:
+                got = [rring.complete(sid, steps - n_chk, n_chk) for sid in range(rring.n_sensors)]
+                if all(g == n_chk for g in got):
+                    break
+            timed_native.ring_report = {"records_expected_per_sensor": n_chk, "records_received": got, "record_bytes": 512,
+                                        "transport": "stores by a kernel of the producing GPU into rank 0's GPU memory (CUDA IPC mapping, NVLink peer access); no NCCL, no host hop"}
         ev1.record()
         barrier()
         ms = ev0.elapsed_time(ev1)
@@ -466,6 +482,16 @@ def main():
                               fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
         config_exec["driver"] = "dms_sequence_run (native host threads)"
         pipe = None
+        # per-frame result exchange of the multi-sensor mode: one ring in rank 0's GPU memory, every rank's trackers publish into it
+        from densemonoslam_b200.ring import ResultRing
+        ring_slots = 1024
+        from densemonoslam_b200 import multi
+        if rank == 0:
+            rring = ResultRing(world, ring_slots, device=local_rank)
+            multi.share_ring_handle(rring.export())
+        else:
+            rring = ResultRing(world, ring_slots, device=local_rank, handle=multi.share_ring_handle(None))
+        rring.attach(seq, rank)
         ms, ktimes, iters_seen, so3_seen, clocks, last = timed_native(seq, args.steps, args.warmup, False)
     else:
         config_exec["driver"] = "python threads over the per-call C ABI"
@@ -474,6 +500,7 @@ def main():
     value = world * args.steps / (ms * 1e-3)
     if native:
         config_exec["host_timeline"] = timed_native.host_timeline
+        result_ring = getattr(timed_native, "ring_report", None)
     gt = frames[(args.steps - 1) % ring]["gt"]
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
     roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, 8) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
@@ -498,11 +525,11 @@ def main():
 
     out = {"metric": "odometry_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": config, "config_exec": config_exec, "roofline": roofline,
+           "config": config, "config_exec": config_exec, "roofline": roofline, "result_ring": result_ring if native else None,
            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": per_frame_in + (0 if (share_rgb and depth > 1) else frames[0]["live"]["rgba"].nbytes),
                    "d2h_bytes_per_step": int(_lib.load().dms_track_d2h_bytes()), "steps": e2e_steps, "last_frame_abs_translation_error_m": pose_err_e2e,
                    "note": "host-buffer C-ABI entry points (pinned inputs), pose result read back every frame"},
-           "gpu_launches": (5 * args.steps + 1) if (share_rgb and depth > 1) else 6 * args.steps,  # per frame: k_populate x2 (x3 when the previous image is reloaded), k_maps_pyramid, k_icp_depth, k_track
+           "gpu_launches": (6 * args.steps + 1) if native else 6 * args.steps,  # per frame: k_populate x2 (x3 when the previous image is reloaded), k_maps_pyramid, k_icp_depth, k_track, k_ring_publish
            "clocks": clocks, "last_frame_abs_translation_error_m": pose_err,
            "lib": os.path.relpath(_lib.LIB_PATH, ROOT)}
     if world > 1:

@@ -67,6 +67,12 @@ class DmsSeqResult(C.Structure):
     _fields_ = [("pose", C.c_float * 16), ("r", DmsResult), ("track_ms", C.c_float)]
 
 
+class DmsRingRecord(C.Structure):
+    _fields_ = [("seq", C.c_uint32), ("sensor", C.c_uint32), ("frame", C.c_uint32), ("reserved", C.c_uint32), ("R", C.c_float * 9), ("t", C.c_float * 3),
+                ("stats", C.c_float * 6), ("iters", C.c_int32 * 3), ("so3_iters", C.c_int32), ("A", C.c_double * 36), ("b", C.c_double * 6),
+                ("pad", C.c_uint8 * 72)]
+
+
 class DmsSeqOptions(C.Structure):
     _fields_ = [("n_trackers", C.c_int), ("block_threads", C.c_int), ("grid", C.c_int), ("wait_mode", C.c_int), ("rgbOnly", C.c_int),
                 ("icpWeight", C.c_float), ("pyramid", C.c_int), ("fastOdom", C.c_int), ("so3", C.c_int), ("depthCutoff", C.c_float),
@@ -149,6 +155,15 @@ SIGNATURES = {
     "dms_sequence_run": (C.c_int, [_P, C.POINTER(DmsSeqFrame), C.c_int, _P, C.c_int, C.POINTER(DmsSeqResult)]),
     "dms_sequence_resident": (C.c_int, [_P]),
     "dms_sequence_host_timeline": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "dms_sequence_attach_ring": (C.c_int, [_P, _P, C.c_int]),
+    "dms_ring_create": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int]),
+    "dms_ring_export": (C.c_int, [_P, C.POINTER(C.c_uint8)]),
+    "dms_ring_open": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int]),
+    "dms_ring_destroy": (C.c_int, [_P]),
+    "dms_ring_clear": (C.c_int, [_P, _P]),
+    "dms_ring_publish": (C.c_int, [_P, _P, C.c_int, C.c_int, _P]),
+    "dms_ring_poll": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), _P]),
+    "dms_ring_read": (C.c_int, [_P, C.c_int, C.c_int, C.POINTER(DmsRingRecord), _P]),
     "dms_version": (C.c_char_p, []),
     "dms_device_count": (C.c_int, []),
     "dms_track_d2h_bytes": (C.c_size_t, []),

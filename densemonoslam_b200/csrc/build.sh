@@ -8,5 +8,5 @@ mkdir -p ../lib
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -fmad=false \
       -Xcompiler -fPIC,-ffp-contract=off -Xptxas -v \
-      -I../../include -I. -shared -o ../lib/libdmsodom.so pyramid.cu track.cu odom_c.cu frontend.cu nid.cu splat.cu sequence.cu "$@"
+      -I../../include -I. -shared -o ../lib/libdmsodom.so pyramid.cu track.cu odom_c.cu frontend.cu nid.cu splat.cu sequence.cu ring.cu "$@"
 echo "built densemonoslam_b200/lib/libdmsodom.so"

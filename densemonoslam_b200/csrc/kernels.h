@@ -63,6 +63,10 @@ struct TrackParams {
 };
 static const int MAX_DBG = 1024;
 
+// accessors of the opaque handle for the other translation units (ring.cu)
+const Ctrl* odom_ctrl_device(const dms_odom* h);
+int odom_device(const dms_odom* h);
+
 void threshold_equiv(float distThres, float angleThres, float* dist2Max, float* sine2Lim);
 int track_block_threads_max();
 int track_block_threads_default();

@@ -115,6 +115,11 @@ int ensure_stage(dms_odom* h) {
 
 }  // namespace
 
+namespace dms {
+const Ctrl* odom_ctrl_device(const dms_odom* h) { return h->ctrl; }
+int odom_device(const dms_odom* h) { return h->device; }
+}  // namespace dms
+
 extern "C" {
 
 const char* dms_version(void) { return "dmsodom 0.1 (sm_100a)"; }

@@ -12,6 +12,7 @@
 #include <vector>
 #include <cuda_runtime.h>
 #include "../../include/dmsodom/sequence_c.h"
+#include "../../include/dmsodom/ring_c.h"
 
 namespace {
 
@@ -43,6 +44,7 @@ struct dms_sequence {
   std::vector<cudaStream_t> streams, copy_streams;
   std::vector<Stage> stages;   // two per tracker, allocated by the first host-buffer run
   int grid, resident;
+  dms_ring* ring = nullptr; int ring_sensor = 0;   // results of every tracked frame also go to this ring (dms_sequence_attach_ring)
   Flags issued, taken;
   // worker pool: one host thread per tracker, created once and parked between runs (spawning them per run cost a
   // fixed ~2 ms per call, which dominated short runs and multi-rank launches)
@@ -144,6 +146,7 @@ static void seq_work(dms_sequence* s, int k) {
       // this tracker's next frame goes up while the current one is tracked (queued behind the first uploads of the other
       // trackers, so a short run starts all of them before it prefetches).  The other stage held frame i - K, whose kernels
       // finished before its result was collected.
+      if (!rc && s->ring) rc = dms_ring_publish(s->ring, h, s->ring_sensor, i, st);   // behind the tracking kernel, device to device
       if (!rc && host && i + K < n) rc = upload(i + K, sg[((i / K) + 1) & 1]);
       if (!rc) {
         long long expect = -1;
@@ -257,6 +260,12 @@ int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const 
   s->timeline[0] = (double)s->t_first_launch_us.load(); s->timeline[1] = (double)s->t_last_collect_us.load();
   s->timeline[2] = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - s->t_entry).count();
   return s->err.load();
+}
+
+int dms_sequence_attach_ring(dms_sequence* s, dms_ring* r, int sensor) {
+  if (!s || sensor < 0) return DMS_ERR_INVALID;
+  s->ring = r; s->ring_sensor = sensor;
+  return DMS_OK;
 }
 
 int dms_sequence_host_timeline(const dms_sequence* s, double us[3]) {

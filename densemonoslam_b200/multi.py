@@ -2,7 +2,8 @@
 ~10 us Gauss-Newton iteration would cost more than the iteration), it shards across sensors -- the
 collaborative mode of the reference (MainController.cpp:226-233, one Context with its own trackers per
 camera).  One process per GPU (torchrun), sensors dealt round-robin to ranks, no collective on the data
-path; the only exchange is the small per-frame result record, gathered after the timed region.
+path; the only exchange is the small per-frame result record: written device-to-device into a ring in rank 0's GPU memory
+(densemonoslam_b200/ring.py; set up with share_ring_handle below), or gathered after the run (gather_records).
 
 Works with any torch.distributed backend (tests use gloo on CPU with a stand-in tracker).
 """
@@ -80,3 +81,20 @@ def _fields(trk, res):
         r = res[2]
         return [r.lastICPError, r.lastICPCount, r.lastRGBError, r.lastRGBCount, r.lastSO3Error, r.lastSO3Count]
     return [trk.lastICPError, trk.lastICPCount, trk.lastRGBError, trk.lastRGBCount, trk.lastSO3Error, trk.lastSO3Count]
+
+
+def share_ring_handle(handle: bytes | None) -> bytes:
+    """The result ring lives in rank 0's GPU memory: rank 0 passes its 64-byte CUDA IPC handle (ResultRing.export()), every
+    rank gets it back (the producers map the ring with it).  One broadcast of 64 bytes at set-up, nothing per frame."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        if handle is None:
+            raise ValueError("the only rank must own the ring")
+        return bytes(handle)
+    if (dist.get_rank() == 0) != (handle is not None):
+        raise ValueError("exactly rank 0 passes a handle")
+    box = [bytes(handle) if handle is not None else None]
+    dist.broadcast_object_list(box, src=0)
+    if not isinstance(box[0], (bytes, bytearray)) or len(box[0]) != 64:
+        raise ValueError("bad ring handle")
+    return bytes(box[0])

@@ -8,7 +8,7 @@ import pytest
 
 from conftest import ROOT
 
-HEADERS = [os.path.join(ROOT, "include", "dmsodom", n) for n in ("odom_c.h", "frontend_c.h", "nid_c.h", "splat_c.h", "sequence_c.h")]
+HEADERS = [os.path.join(ROOT, "include", "dmsodom", n) for n in ("odom_c.h", "frontend_c.h", "nid_c.h", "splat_c.h", "sequence_c.h", "ring_c.h")]
 
 
 def declared_symbols():

@@ -38,6 +38,10 @@ def _worker(rank, world, port, outfile):
     mine = multi.assign_sensors(N_SENSORS, world, rank)
     local = multi.run_sensors(_make_tracker, {sid: _sensor_frames(sid)[1] for sid in mine}, FLAGS)
     full = multi.gather_records(local, N_SENSORS, N_FRAMES)
+    # set-up of the result ring: rank 0's 64-byte handle reaches every rank unchanged
+    handle = bytes(range(64))
+    got = multi.share_ring_handle(handle if rank == 0 else None)
+    assert got == handle
     if rank == 0:
         np.save(outfile, full)
     dist.barrier()
