@@ -30,6 +30,10 @@ import time
 
 import numpy as np
 
+# Trackers sharing a GPU run on one stream each; streams beyond the number of hardware queues (8 by default) alias and
+# serialise.  Must be set before CUDA starts.  (The library sizes its tracking kernels by this variable.)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -210,7 +214,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 8, fewer for short runs so that every tracker gets several frames)")
+    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 12, fewer for short runs so that every tracker gets two frames or more)")
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 768)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -222,7 +226,7 @@ def main():
 
     if args.wait < 0:
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
-        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else 8) > len(os.sched_getaffinity(0)) else 2
+        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else 12) > len(os.sched_getaffinity(0)) else 2
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -293,7 +297,7 @@ def main():
             if threads:
                 h.set_block(threads)
             per_sm = max(1, 1024 // threads) if threads else 1
-            h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // min(depth, 8)))  # at most 8 kernels resident; further trackers queue and take the slots as they free up
+            h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // min(depth, int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8")))))  # as many kernels resident as there are hardware queues; further trackers queue
             h.set_wait(args.wait if depth > 1 else 0)   # trackers sharing the GPU: do not burn a host core per tracker while waiting
             h.set_timing(1)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
@@ -465,12 +469,13 @@ def main():
                 "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
-    # trackers sharing the GPU: 8 in a long run; a short run (the driver's 20 steps) fills and drains the pipeline once, which
+    # trackers sharing the GPU: 12 in a long run; a short run (the driver's 20 steps) fills and drains the pipeline once, which
     # costs less with fewer, larger trackers (measured: tools/quick_perf.py)
-    depth = max(1, args.pipeline) if args.pipeline else min(8, max(2, args.steps // 3))
+    depth = max(1, args.pipeline) if args.pipeline else min(12, max(2, args.steps // 2))
     depth_e2e = max(1, args.pipeline) if args.pipeline else min(6, max(2, args.steps // 5))   # uploads inside the region: PCIe-bound, fewer trackers start sooner
     _thr = args.threads if args.threads else 768
-    _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, 8)
+    _queues = int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8"))
+    _grid = args.grid if args.grid else (sms * max(1, 1024 // _thr)) // min(depth, _queues)
     config_exec["pipeline"] = (f"{depth} trackers share the GPU ({_grid} blocks of {_thr} threads each, own stream); frame f runs on tracker f % {depth}"
                           if depth > 1 else "single tracker, frames strictly one after another")
     native = depth > 1 and args.driver == "native" and share_rgb
@@ -503,7 +508,7 @@ def main():
         result_ring = getattr(timed_native, "ring_report", None)
     gt = frames[(args.steps - 1) % ring]["gt"]
     pose_err = float(np.max(np.abs(last[0] - gt[:3, 3])))
-    roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, 8) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
+    roofline = roofline_of(ms, args.steps, ktimes, iters_seen, so3_seen, min(depth, _queues) if not args.grid else min(depth, max(1, (sms * max(1, 1024 // _thr)) // args.grid)))
 
     if args.quick:
         if rank == 0:
