@@ -299,7 +299,7 @@ def main():
             per_sm = max(1, 1024 // threads) if threads else 1
             h.set_grid(args.grid if args.grid else (0 if depth == 1 else (sms * per_sm) // min(depth, int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8")))))  # as many kernels resident as there are hardware queues; further trackers queue
             h.set_wait(args.wait if depth > 1 else 0)   # trackers sharing the GPU: do not burn a host core per tracker while waiting
-            h.set_timing(1)
+            h.set_timing(3)   # CUDA events around the kernel only: the production build of k_track (mode 1 = instrumented build with phase counters)
             hs.append(h); ss.append(torch.cuda.Stream(device=local_rank) if depth > 1 else torch.cuda.current_stream())
         return hs, ss
 
@@ -484,7 +484,7 @@ def main():
         from densemonoslam_b200.sequence import SequenceTracker
         seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth, block_threads=args.threads,
                               grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
-                              fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
+                              fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=3)
         config_exec["driver"] = "dms_sequence_run (native host threads)"
         pipe = None
         # per-frame result exchange of the multi-sensor mode: one ring in rank 0's GPU memory, every rank's trackers publish into it
@@ -520,7 +520,7 @@ def main():
             del seq
             seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=depth_e2e, block_threads=args.threads,
                                   grid=args.grid, wait_mode=args.wait, rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]),
-                                  fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=1)
+                                  fastOdom=int(FLAGS["fastOdom"]), so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=3)
         config_exec["pipeline_e2e"] = f"{depth_e2e} trackers, each with two input stages on the device and a copy stream (frame f + {depth_e2e} uploads under frame f's kernels)"
         ms_e2e, _, _, _, _, last_e2e = timed_native(seq, e2e_steps, min(args.warmup, 5), True)
     else:
@@ -554,7 +554,12 @@ def main():
         n1 = min(args.steps, 300)
         ms1, k1, it1, s31, _, _ = timed(pipe1, n1, args.warmup, False)
         lat = np.sort(np.array(timed.latencies))
+        track_us = float(np.mean([p_["track"] for p_ in timed.phases])) * 1e3
+        # phase breakdown: a short second run on the instrumented build of the kernel (about 3 % slower), outside the numbers above
+        pipe1[0][0].set_timing(1)
+        timed(pipe1, min(n1, 40), 3, False)
         ph = {k: float(np.mean([p_[k] for p_ in timed.phases])) * 1e3 for k in timed.phases[0]}
+        ph["track_instrumented"] = ph.get("track"); ph["track"] = track_us
         gn_its = max(1, int(np.mean([sum(it) for it in it1])))
         out["latency"] = {"value": world * n1 / (ms1 * 1e-3), "unit": "frames/s", "ms_per_frame": ms1 / n1, "frames": n1,
                           "mode": "one tracker per GPU, one frame in flight, inputs resident in HBM",

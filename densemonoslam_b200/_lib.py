@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libdmsodom.so")
+LIB_PATH = os.environ.get("DMSODOM_LIB") or os.path.join(_HERE, "lib", "libdmsodom.so")  # DMSODOM_LIB: another build of the same library (A/B timing of kernel variants)
 REPO_ROOT = os.path.dirname(_HERE)
 
 

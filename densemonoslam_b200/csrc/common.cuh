@@ -86,8 +86,10 @@ struct Exact {
   long long hi, lo;
   int bad;
   __device__ __forceinline__ void clear() { hi = 0; lo = 0; bad = 0; }
+  // branch-free: a value that sets `bad` also adds a saturated / zero conversion, which no longer matters (the result
+  // of a flagged accumulator is NaN)
   __device__ __forceinline__ void addf(float p) {
-    if (!(fabsf(p) < 4.611686018427387904e18f)) { bad = 1; return; }
+    bad |= !(fabsf(p) < 4.611686018427387904e18f) ? 1 : 0;
     const float hf = truncf(p);
     hi += __float2ll_rz(hf);
     lo += __float2ll_rz(fmul(fsub(p, hf), 17592186044416.0f));

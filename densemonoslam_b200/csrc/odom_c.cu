@@ -275,7 +275,7 @@ int dms_odom_set_block(dms_odom* h, int threads) {
 }
 int dms_odom_set_wait(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 3) return DMS_ERR_INVALID; h->blocking_wait = mode; h->wait_ema_us = 0.0; return DMS_OK; }
 int dms_odom_set_numerics(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 1) return DMS_ERR_INVALID; h->legacy = mode; return DMS_OK; }
-int dms_odom_set_timing(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 2) return DMS_ERR_INVALID; h->timing = mode; return DMS_OK; }
+int dms_odom_set_timing(dms_odom* h, int mode) { if (!h || mode < 0 || mode > 3) return DMS_ERR_INVALID; h->timing = mode; return DMS_OK; }
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out) { if (!h || !out) return DMS_ERR_INVALID; *out = h->last_timing; return DMS_OK; }
 
 // ------------------------------------------------------------------ pyramid construction
@@ -428,7 +428,7 @@ int dms_odom_track_async(dms_odom* h, const float trans[3], const float rot[9], 
     mat3_inv_host<double>(Kd, Ki);
     memcpy(P.Kd[i], Kd, sizeof Kd); memcpy(P.Kinv[i], Ki, sizeof Ki);
   }
-  P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = h->timing;
+  P.ctrl = h->ctrl; P.sync = h->sync; P.acc = h->acc; P.trace = h->tracing ? h->trace : nullptr; P.timing = (h->timing == 1 || h->timing == 2) ? h->timing : 0;  // mode 3: events only, production kernel
   P.dbg = h->timing >= 2 ? h->dbg : nullptr;  // the timeline probes run only on request (set_timing(h, 2))
   P.seglist = h->seglist;
   if (h->timing >= 2) CK(cudaMemsetAsync(h->dbg, 0, sizeof(unsigned long long) * 2 * MAX_DBG, s));
@@ -483,6 +483,12 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
   if (h->timing) {
     float ms = 0.f; cudaEventElapsedTime(&ms, h->ev0, h->ev1);
     h->last_timing.track_ms = ms;
+    if (h->timing == 3) {  // events only: the production kernel keeps no phase counters
+      const float ms_ = h->last_timing.track_ms;
+      memset(&h->last_timing, 0, sizeof h->last_timing);
+      h->last_timing.track_ms = ms_;
+      return DMS_OK;
+    }
     h->last_timing.so3Step_ms = (float)(C->t_so3 * 1e-6);
     h->last_timing.icpStep_ms = (float)(C->t_phaseA * 1e-6);  // ICP rows + photometric residual are one fused pass
     h->last_timing.computeRgbResidual_ms = 0.f;

@@ -97,7 +97,9 @@ int dms_odom_set_wait(dms_odom* h, int mode);
 enum dms_numerics { DMS_NUMERICS_IEEE = 0, DMS_NUMERICS_LEGACY = 1 };
 int dms_odom_set_numerics(dms_odom* h, int mode);
 /* mode 0 = off (default), 1 = CUDA events around the kernel + per-phase counters of thread block 0 (a few clock reads per
- * phase), 2 = additionally the {tag, timestamp} timeline read by dms_odom_get_timeline (a memset per track). */
+ * phase), 2 = additionally the {tag, timestamp} timeline read by dms_odom_get_timeline (a memset per track), 3 = the CUDA
+ * events only (track_ms; the other fields read 0).  Modes 1 and 2 (and dms_odom_set_trace) run the instrumented build of
+ * the tracking kernel, which is about 3 % slower than the production build that modes 0 and 3 run. */
 int dms_odom_set_timing(dms_odom* h, int mode);
 int dms_odom_get_timing(const dms_odom* h, dms_odom_timing* out);
 

@@ -47,7 +47,7 @@ for cfg in cfgs:
     trackers, threads = parts[0], parts[1]
     grid = parts[2] if len(parts) > 2 else 0
     seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, n_trackers=trackers, block_threads=threads if trackers > 1 or threads != 1024 else 0,
-                          grid=grid, wait_mode=2 if trackers > 1 else 0, timing=1)
+                          grid=grid, wait_mode=2 if trackers > 1 else 0, timing=int(os.environ.get("QP_TIMING", "3")))
     first_prev = dev[-1]["li"]
     seq.run(seq.make_frames(frame_list(3 * trackers)), first_prev, HOST)
     fc = seq.make_frames(frame_list(steps))
