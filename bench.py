@@ -214,7 +214,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 12, fewer for short runs so that every tracker gets two frames or more)")
+    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 20, fewer for short runs so that every tracker gets two frames or more)")
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 768)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -226,7 +226,7 @@ def main():
 
     if args.wait < 0:
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
-        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else 12) > len(os.sched_getaffinity(0)) else 2
+        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else min(20, max(2, args.steps // 2))) > len(os.sched_getaffinity(0)) else 2
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -469,9 +469,10 @@ def main():
                 "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
-    # trackers sharing the GPU: 12 in a long run; a short run (the driver's 20 steps) fills and drains the pipeline once, which
-    # costs less with fewer, larger trackers (measured: tools/quick_perf.py)
-    depth = max(1, args.pipeline) if args.pipeline else min(12, max(2, args.steps // 2))
+    # trackers sharing the GPU: 20 in a long run (measured, tools/quick_perf.py at 300 frames: 12 x 24 blocks 5500 frames/s,
+    # 20 x 14 blocks 5900, 28 x 10 5950); a short run (the driver's 20 steps) fills and drains the pipeline once, which costs
+    # less with fewer, larger trackers that get two frames each (10 x 29: 5080 at 20 frames, 20 x 14: 4300 - 5300)
+    depth = max(1, args.pipeline) if args.pipeline else min(20, max(2, args.steps // 2))
     depth_e2e = max(1, args.pipeline) if args.pipeline else min(6, max(2, args.steps // 5))   # uploads inside the region: PCIe-bound, fewer trackers start sooner
     _thr = args.threads if args.threads else 768
     _queues = int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8"))
