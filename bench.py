@@ -190,6 +190,70 @@ def run_legacy_frames(cam, frames, n_frames, budget_s):
 _REAL_STDOUT = None
 
 
+def run_frontend_e2e(cam, steps, device):
+    """Frame-to-model variant of the end-to-end leg: what a caller of the reference really uploads per
+    frame is the sensor frame (RGBA8 + u16 depth, 6 B per pixel); the model view is predicted on the device from the surfel
+    map (dms_splat_predict = IndexMap::combinedPredict) and the frame runs through the processFrame-shaped front end
+    (dms_frontend_process: depth filter, prediction, FillIn / denseEnough, frame-to-model track with the previous pose as
+    the prior).  One frame in flight by construction: frame f + 1 is predicted from the pose of frame f.  Returns the block
+    reported as `e2e_frontend`."""
+    import torch
+    from densemonoslam_b200 import splat, synth
+    from densemonoslam_b200.frontend import TrackingFrontEnd
+    scene = synth.street_scene(2021)
+    n_ring = 8
+    poses, T = [], np.eye(4)
+    for f in range(n_ring):  # slow forward motion with a little yaw: the three map views below cover all of it
+        T = T @ synth.pose_from((0.0, np.deg2rad(0.15) * np.sin(f * 0.7), 0.0), (0.002 * np.cos(f), 0.0, 0.03))
+        poses.append(T.copy())
+    S = np.concatenate([synth.surfels_from_view(synth.render(scene, cam, poses[k], seed=77 + k, max_depth=60.0, hole_frac=0.0, zero_frac=0.0), poses[k], cam, time=1)
+                        for k in (0, 3, 7)])
+    d_S = torch.from_numpy(S).to(device)
+    lives = [synth.render(scene, cam, poses[f], seed=300 + f, max_depth=60.0, depth_noise=0.004) for f in range(n_ring)]
+    pin = [(torch.from_numpy(l["rgba"]).pin_memory(), torch.from_numpy(l["depth"]).pin_memory()) for l in lives]
+    d_rgba = [torch.empty_like(pin[0][0], device=device) for _ in range(2)]
+    d_depth = [torch.empty_like(pin[0][1], device=device) for _ in range(2)]
+    c = (cam.cx, cam.cy, cam.fx, cam.fy)
+
+    def predictor(pose, kind, tick):
+        img, ver, nor, _ = splat.combinedPredict(d_S, pose, c, cam.height, cam.width, 25.0, 5.0, 2, 0, 2, 200, splat.ACTIVE)
+        return {"vertex": ver, "normal": nor, "image": img}
+
+    fe = TrackingFrontEnd(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, predictor, device=device.index or 0, depthCutoff=25.0, closeLoops=0)
+    order = list(range(n_ring)) + list(range(n_ring - 2, 0, -1))   # there and back again: the motion stays continuous when the ring wraps
+
+    def frame(i, first=False):
+        k = order[i % len(order)]
+        b = i & 1
+        d_rgba[b].copy_(pin[k][0], non_blocking=True); d_depth[b].copy_(pin[k][1], non_blocking=True)
+        return k, fe.process(d_rgba[b], d_depth[b], poses[k].astype(np.float32) if first else None)
+
+    frame(0, True)
+    for i in range(1, 4):
+        frame(i)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    ok = 0
+    for i in range(4, 4 + steps):
+        k, r = frame(i)
+        ok += int(r["tracked"] and r["trackingOk"])
+    ev1.record(); torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    err = float(np.max(np.abs(r["pose"][:3, 3] - poses[k][:3, 3])))
+    return {"value": steps / (ms * 1e-3), "unit": "frames/s", "ms_per_frame": ms / steps, "steps": steps,
+            "h2d_bytes_per_step": int(pin[0][0].numel() * pin[0][0].element_size() + pin[0][1].numel() * pin[0][1].element_size()),
+            "d2h_bytes_per_step": int(_lib_track_d2h()), "surfels": int(len(S)), "frames_tracked": ok,
+            "last_frame_abs_translation_error_m": err,
+            "note": "sensor frame uploaded from pinned host memory, model view predicted on the device from the surfel map, "
+                    "front end with the previous pose as the prior; one frame in flight; the Python callback of the predictor is inside the timed region"}
+
+
+def _lib_track_d2h():
+    from densemonoslam_b200 import _lib
+    return _lib.load().dms_track_d2h_bytes()
+
+
 def _guard_stdout():
     """Libraries (NCCL's version banner, OpenMP) may write to fd 1; the contract is ONE JSON line on stdout.  Everything
     else goes to stderr, the JSON line to the saved descriptor."""
@@ -570,6 +634,11 @@ def main():
                           "us_per_gn_iteration": (ph.get("icpStep", 0.0) + ph.get("rgbStep", 0.0) + ph.get("computeRgbResidual", 0.0)) / gn_its,
                           "roofline": roofline_of(ms1, n1, k1, it1, s31, 1)}
 
+    if rank == 0 and world == 1 and args.workload == "kitti":
+        try:
+            out["e2e_frontend"] = run_frontend_e2e(cam, min(args.steps, 100), torch.device("cuda", local_rank))
+        except Exception as e:  # reported, never fatal for the contract line
+            out["e2e_frontend"] = {"unavailable": f"{type(e).__name__}: {e}"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         host_frames = frames[: min(ring, 4)]
         run_oracle_frames(cam, host_frames, 1, 30.0)

@@ -25,7 +25,7 @@ struct Level {
   unsigned char *lastImage, *nextImage, *lastNextImage;
   short *dIdx, *dIdy;
   unsigned short* depth_tmp;
-  uint2* corr;  // 8-byte compact DataTerm {s16 u0, s16 v0, s16 diff, u8 valid, u8 0}
+  uint4* corr;  // 16-byte DataTerm {s16 u0, s16 v0, s16 diff, u8 valid, u8 0, f32 z = model depth at (u0, v0), u32 0}
   int pitch_f32, pitch_u8, pitch_s16, pitch_u16, pitch_corr;
 };
 

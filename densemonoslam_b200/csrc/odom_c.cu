@@ -178,7 +178,7 @@ int dms_odom_create(dms_odom** out, int device, int width, int height, float cx,
     L.pitch_u8 = (int)align_up((size_t)L.cols, 256);
     L.pitch_s16 = (int)align_up((size_t)L.cols * 2, 256);
     L.pitch_u16 = L.pitch_s16;
-    L.pitch_corr = (int)align_up((size_t)L.cols * 8, 256);
+    L.pitch_corr = (int)align_up((size_t)L.cols * 16, 256);
     const size_t map = (size_t)3 * L.rows * L.pitch_f32, img = (size_t)L.rows * L.pitch_u8;
     want((void**)&L.vmap_curr, map); want((void**)&L.nmap_curr, map); want((void**)&L.vmap_prev, map); want((void**)&L.nmap_prev, map);
     want((void**)&L.lastDepth, (size_t)L.rows * L.pitch_f32); want((void**)&L.nextDepth, (size_t)L.rows * L.pitch_f32);
@@ -661,7 +661,7 @@ int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t*
     case DMS_BUF_DIDX: p = L.dIdx; pb = L.pitch_s16; e = 2; break;
     case DMS_BUF_DIDY: p = L.dIdy; pb = L.pitch_s16; e = 2; break;
     case DMS_BUF_DEPTH_TMP: p = L.depth_tmp; pb = L.pitch_u16; e = 2; break;
-    case DMS_BUF_CORRES: p = L.corr; pb = L.pitch_corr; e = 8; break;
+    case DMS_BUF_CORRES: p = L.corr; pb = L.pitch_corr; e = 16; break;
     case DMS_BUF_NEXT_DEPTH_MASKED: p = L.nextDepthMasked; pb = L.pitch_f32; break;
     default: return fail(h, DMS_ERR_INVALID, "get_buffer: unknown buffer");
   }

@@ -14,7 +14,7 @@ from . import _lib
 
 BUF = {"vmap_curr": 0, "nmap_curr": 1, "vmap_g_prev": 2, "nmap_g_prev": 3, "lastDepth": 4, "nextDepth": 5, "lastImage": 6,
        "nextImage": 7, "lastNextImage": 8, "dIdx": 9, "dIdy": 10, "depth_tmp": 11, "corr": 12, "nextDepthMasked": 13}
-CORR_DTYPE = np.dtype([("u0", "<i2"), ("v0", "<i2"), ("diff", "<i2"), ("valid", "u1"), ("pad", "u1")])
+CORR_DTYPE = np.dtype([("u0", "<i2"), ("v0", "<i2"), ("diff", "<i2"), ("valid", "u1"), ("pad", "u1"), ("z", "<f4"), ("pad2", "<u4")])
 _BUF_DT = {0: np.float32, 1: np.float32, 2: np.float32, 3: np.float32, 4: np.float32, 5: np.float32, 6: np.uint8, 7: np.uint8,
            8: np.uint8, 9: np.int16, 10: np.int16, 11: np.uint16, 12: CORR_DTYPE, 13: np.float32}
 

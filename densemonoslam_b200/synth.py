@@ -279,3 +279,31 @@ def kitti_sequence(cam: Camera, n_frames: int, *, seed=2021, step=0.8, yaw_deg=0
         live = render(scene, cam, T, seed=seed + 2 * f + 1, max_depth=60.0, depth_noise=depth_noise)
         frames.append({"model": model, "live": live, "prior": prior.astype(np.float32), "gt": T.astype(np.float32)})
     return frames
+
+
+SURFEL_FLOATS = 15  # include/dmsodom/splat_c.h: pos.xyz conf | colour (encoded rgb, -, initTime, -) | times[3] | normal.xyz radius
+
+
+def surfels_from_view(view: dict, T_wc: np.ndarray, cam: Camera, *, time=1, conf=10.0) -> np.ndarray:
+    """A surfel map to predict model views from (bench.py's front-end leg): one surfel per valid pixel of a rendered view,
+    position and normal moved to the world by `T_wc`, radius as Shaders/surfels.glsl:18-35 (getRadius), colour packed as
+    Shaders/color.glsl:18-25 (encodeColor), layout of Vertex.cpp:49-50."""
+    v = view["vmap4"][..., :3].reshape(-1, 3).astype(np.float64)
+    n = view["nmap4"][..., :3].reshape(-1, 3).astype(np.float64)
+    ok = np.isfinite(v).all(1) & np.isfinite(n).all(1) & (v[:, 2] > 0) & (np.abs(n).sum(1) > 0)
+    v, n = v[ok], n[ok]
+    c = view["rgba"].reshape(-1, 4)[ok].astype(np.int64)
+    R, t = np.asarray(T_wc, np.float64)[:3, :3], np.asarray(T_wc, np.float64)[:3, 3]
+    mean_focal = (1.0 / abs(cam.fx) + 1.0 / abs(cam.fy)) / 2.0
+    radius = v[:, 2] * mean_focal * 1.41421356237
+    radius = np.minimum(2.0 * radius, radius / np.maximum(np.abs(n[:, 2]), 1e-6))
+    S = np.zeros((len(v), SURFEL_FLOATS), np.float32)
+    S[:, 0:3] = v @ R.T + t
+    S[:, 3] = conf
+    S[:, 4] = ((c[:, 0] << 16) + (c[:, 1] << 8) + c[:, 2]).astype(np.float32)
+    S[:, 6] = time
+    S[:, 8:11] = -3.0
+    S[:, 8] = time
+    S[:, 11:14] = n @ R.T
+    S[:, 14] = radius
+    return S

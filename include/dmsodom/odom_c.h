@@ -167,7 +167,7 @@ enum dms_buffer {
   DMS_BUF_VMAP_CURR = 0, DMS_BUF_NMAP_CURR = 1, DMS_BUF_VMAP_G_PREV = 2, DMS_BUF_NMAP_G_PREV = 3,
   DMS_BUF_LAST_DEPTH = 4, DMS_BUF_NEXT_DEPTH = 5, DMS_BUF_LAST_IMAGE = 6, DMS_BUF_NEXT_IMAGE = 7,
   DMS_BUF_LAST_NEXT_IMAGE = 8, DMS_BUF_DIDX = 9, DMS_BUF_DIDY = 10, DMS_BUF_DEPTH_TMP = 11,
-  DMS_BUF_CORRES = 12, /* 8-byte records {i16 u0, i16 v0, i16 diff, u8 valid, u8 0}: compact DataTerm, types.cuh:76-82 */
+  DMS_BUF_CORRES = 12, /* 16-byte records {i16 u0, i16 v0, i16 diff, u8 valid, u8 0, f32 z, u32 0}: DataTerm, types.cuh:76-82, plus the model depth at (u0, v0) */
   DMS_BUF_NEXT_DEPTH_MASKED = 13 /* nextDepth with NaN where the iteration-invariant tests of reduce.cu:777-801 fail */
 };
 int dms_odom_get_buffer(dms_odom* h, int which, int level, void** d_ptr, size_t* pitch_bytes, int* rows, int* cols,
