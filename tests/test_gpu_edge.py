@@ -210,3 +210,29 @@ def test_full_track_parity_in_the_shared_gpu_launch_shape(torch_cuda, orc, synth
         prior = f["prior"]
         load_frame_to_model(torch_cuda, g, o, f["model"], f["live"], prior)
         compare_track(g, o, prior[:3, 3].copy(), prior[:3, :3].copy(), FLAG_ROWS["frameToModel"])
+
+
+@pytest.mark.parametrize("row", ["frameToModel", "frameToModel_fastOdom_nopyr", "modelToModel", "rgbOnly", "icpOnly_w100", "referenceFrame"])
+@pytest.mark.parametrize("shape", [(0, 0), (14, 512)])
+def test_production_build_of_the_tracking_kernel(torch_cuda, orc, synth, row, shape):
+    """The parity tests above run the instrumented build of k_track (they read its per-iteration trace).  The build a
+    caller gets -- no trace, timing off or events only -- is a separate instantiation of the same body: its final pose,
+    counts, errors and last system must equal the oracle's as well, alone on the GPU and in the launch shape of trackers
+    that share it."""
+    from densemonoslam_b200.odometry import RGBDOdometry, DEFAULT_ANGLE_THRESH
+    cam = synth.CAM_KITTI if shape[0] else synth.CAM_VGA
+    frames = synth.kitti_sequence(cam, 2, seed=2021)
+    o = orc.OracleOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, 0.10, DEFAULT_ANGLE_THRESH)
+    for mode in (0, 3):
+        g = RGBDOdometry(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, 0.10, DEFAULT_ANGLE_THRESH)
+        g.set_timing(mode)
+        if shape[0]:
+            g.set_block(shape[1]); g.set_grid(shape[0])
+        g.initFirstRGB(to_dev(torch_cuda, frames[0]["live"]["rgba"])); o.initFirstRGB(frames[0]["live"]["rgba"])
+        for f in frames:
+            prior = f["prior"]
+            load_frame_to_model(torch_cuda, g, o, f["model"], f["live"], prior)
+            compare_track(g, o, prior[:3, 3].copy(), prior[:3, :3].copy(), FLAG_ROWS[row], check_trace=False)
+            if mode == 3:
+                tm = g.timing()
+                assert tm["track"] > 0 and tm["icpStep"] == 0 and tm["rgbStep"] == 0   # events only: no phase counters
