@@ -234,7 +234,8 @@ int dms_depth_metric(const uint16_t* d_raw, size_t pitch_in, int rows, int cols,
  * the library, present on every GPU that loads it until the process exits.  Consequences:
  *  - the call performs no cudaMalloc / cudaFree and uses no allocating library routine;
  *  - images above DMS_NOALLOC_MAX_PIXELS pixels, or with more than DMS_NOALLOC_MAX_DIM rows or columns (the same
- *    per-dimension limit as dms_odom_create), are refused with DMS_ERR_TOO_LARGE (and a line on stderr);
+ *    per-dimension limit as dms_odom_create), or whose maps span more than 4 GB (3 * rows * pitch_bytes: the kernels
+ *    address a map's planes with 32-bit byte offsets), are refused with DMS_ERR_TOO_LARGE (and a line on stderr);
  *  - all calls on one GPU share the array, which is cleared at the start of every call: two calls
  *    whose GPU work overlaps (different streams, or different host threads) race on it and give
  *    wrong sums -- serialise them;
