@@ -47,3 +47,5 @@ def test_our_arm_line():
     assert True and j["value"] > 0 and "workload" in j["config"]
     assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(j["clocks"])
     assert j["last_frame_abs_translation_error_m"] < 0.05 and e["last_frame_abs_translation_error_m"] < 0.05   # the tracker pulls the 3 cm prior onto the ground truth
+    fe = j["e2e_frontend"]   # sensor frame uploaded, model view predicted on the device: every frame tracked, pose on the ground truth
+    assert fe["value"] > 0 and fe["frames_tracked"] == fe["steps"] and 2e6 < fe["h2d_bytes_per_step"] < 4e6 and fe["last_frame_abs_translation_error_m"] < 0.03

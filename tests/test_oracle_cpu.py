@@ -235,3 +235,16 @@ def test_splat_restatement_pieces():
     unseen = surfel(0, 0, 2, 0.1, 1, t=-3.0)
     assert not (sr.predict(np.stack([unseen]), **args)[1][..., 2] > 0).any()
     assert (sr.predict(np.stack([unseen]), **{**args, "active": 0})[1][..., 2] > 0).any()   # INACTIVE keeps -3 surfels (splat.vert:46)
+
+
+def test_synthetic_surfel_map_matches_the_checker_helper(synth):
+    """bench.py's front-end leg builds its surfel map with synth.surfels_from_view (the product side may not touch oracle/);
+    it must lay the 15 floats out exactly as the helper the splat parity tests use."""
+    from oracle import splat_ref as sr
+    cam = synth.scaled_camera(synth.CAM_VGA, 4)
+    T = synth.pose_from((0.02, -0.03, 0.01), (0.1, -0.05, 0.2))
+    view = synth.render(synth.room_scene(5), cam, T, seed=9, hole_frac=0.02)
+    a = synth.surfels_from_view(view, T, cam, time=3, conf=10.0)
+    b = sr.surfels_from_view(view["vmap4"], view["nmap4"], view["rgba"], T, (cam.cx, cam.cy, cam.fx, cam.fy), time=3, sensor=0, conf=10.0)
+    assert a.shape == b.shape and a.shape[1] == synth.SURFEL_FLOATS == sr.SURFEL_FLOATS and len(a) > 1000
+    assert np.array_equal(a, b)
