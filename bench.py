@@ -115,6 +115,9 @@ class ClockSampler(threading.Thread):
         nv = self.nv
         names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        # the first query waits until the trackers' launches of the first round are out: an NVML call takes driver locks, and
+        # one that coincides with the launches at the start of a 4 ms timed region was seen to cost the region 0.8 ms
+        time.sleep(float(os.environ.get("DMS_CLOCK_SAMPLER_DELAY_S", "0.0012")))
         while not self.stop_flag:
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))

@@ -47,18 +47,18 @@ for cfg in cfgs:
     trackers, threads = parts[0], parts[1]
     grid = parts[2] if len(parts) > 2 else 0
     seq = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, n_trackers=trackers, block_threads=threads if trackers > 1 or threads != 1024 else 0,
-                          grid=grid, wait_mode=2 if trackers > 1 else 0, timing=int(os.environ.get("QP_TIMING", "3")))
+                          grid=grid, wait_mode=int(os.environ.get("QP_WAIT", "2")) if trackers > 1 else 0, timing=int(os.environ.get("QP_TIMING", "3")))
     first_prev = dev[-1]["li"]
     seq.run(seq.make_frames(frame_list(3 * trackers)), first_prev, HOST)
     fc = seq.make_frames(frame_list(steps))
     torch.cuda.synchronize()
-    best = None
-    for rep in range(3):
+    best = None; alls = []
+    for rep in range(int(os.environ.get("QP_REPS", "3"))):
         t0 = time.perf_counter()
         res = seq.run(fc, first_prev, HOST)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
-        best = dt if best is None or dt < best else best
+        best = dt if best is None or dt < best else best; alls.append(round(steps / dt))
     k_ms = float(np.mean([r.track_ms for r in res]))
-    print(f"{name} {"host" if HOST else "dev"} {cfg:>12s}: {steps / best:8.0f} frames/s  k_track {k_ms * 1000:7.1f} us  resident {seq.resident}", flush=True)
+    print(f"{name} {"host" if HOST else "dev"} {cfg:>12s}: {steps / best:8.0f} frames/s  k_track {k_ms * 1000:7.1f} us  resident {seq.resident}  all {alls}", flush=True)
     del seq
