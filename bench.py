@@ -347,6 +347,7 @@ def main():
                                                                           ("mi", f["model"]["rgba"]), ("d", f["live"]["depth"]), ("li", f["live"]["rgba"]))})
     config_exec["ring_frames"] = ring
     config_exec["cache"] = f"inputs cycle through {ring} distinct resident frames = {ring * per_frame_in / 1e6:.0f} MB (> 126 MB L2)"
+    config_exec["warmup"] = "W frames per tracker, repeated until 0.25 s of untimed work have passed (clock ramp of a fresh process)"
 
     props = torch.cuda.get_device_properties(local_rank)
     sms = props.multi_processor_count
@@ -414,7 +415,16 @@ def main():
             return [{"v": src[i % ring]["v"], "n": src[i % ring]["n"], "mi": src[i % ring]["mi"], "d": src[i % ring]["d"], "li": src[i % ring]["li"],
                      "prior": frames[i % ring]["prior"]} for i in range(n)]
         first_prev = src[(0 - 1) % ring]["li"]
-        seq.run(seq.make_frames(frame_list(max(3, warmup) * max(1, seq.options.n_trackers))), first_prev, host)
+        # warm-up: W frames per tracker, repeated until the GPU has been busy for a quarter of a second -- a fresh process finds
+        # the GPU at its idle clock, and a 10 ms warm-up in front of a 4 ms timed region was seen to leave the region 5 - 20 %
+        # slow on some boxes (clock ramp, first touch of the trackers' memory)
+        wf = seq.make_frames(frame_list(max(3, warmup) * max(1, seq.options.n_trackers)))
+        t_w = time.perf_counter()
+        while True:
+            seq.run(wf, first_prev, host)
+            torch.cuda.synchronize()
+            if time.perf_counter() - t_w > 0.25:
+                break
         fc = seq.make_frames(frame_list(steps))
         rring = getattr(seq, "_ring", None)
         if rring is not None and rring.owner:
@@ -467,8 +477,13 @@ def main():
     def timed(pipe, steps, warmup, host):
         hs, ss = pipe
         depth = len(hs)
-        for i in range(max(3, warmup) * depth):
-            one_frame(hs[i % depth], ss[i % depth], i, host)
+        t_w = time.perf_counter()
+        while True:   # see timed_native: W frames per tracker, for at least a quarter of a second
+            for i in range(max(3, warmup) * depth):
+                one_frame(hs[i % depth], ss[i % depth], i, host)
+            torch.cuda.synchronize()
+            if time.perf_counter() - t_w > 0.25:
+                break
         barrier()
         sampler = ClockSampler(local_rank)
         sampler.start()
