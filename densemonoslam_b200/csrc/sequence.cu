@@ -7,6 +7,7 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <thread>
@@ -17,12 +18,23 @@
 
 namespace {
 
-struct Flags {  // monotone per-frame flags, waited on by other threads
-  std::mutex m; std::condition_variable cv; std::vector<char> f;
-  void reset(size_t n) { std::lock_guard<std::mutex> l(m); f.assign(n, 0); }
-  void set(size_t i) { { std::lock_guard<std::mutex> l(m); f[i] = 1; } cv.notify_all(); }
-  void wait(size_t i, const std::atomic<int>& err) { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return f[i] || err.load(); }); }
-  void wake() { cv.notify_all(); }
+// Monotone per-frame flags.  Every flag has exactly one waiter (the thread of the tracker that needs it), so each tracker
+// thread owns a mutex / condition variable pair and a setter wakes that thread alone: with one shared condition variable
+// every set woke all the trackers' threads, which hurts when the ranks of a box have more tracker threads than cores.
+struct Flags {
+  struct Lane { std::mutex m; std::condition_variable cv; };
+  std::unique_ptr<Lane[]> lanes; size_t n_lanes = 0; std::vector<char> f;
+  void reset(size_t n, size_t k) {
+    if (k != n_lanes) { lanes.reset(new Lane[k]); n_lanes = k; }
+    f.assign(n, 0);   // no run is in progress: the workers are parked
+  }
+  void set(size_t i, size_t waiter) { Lane& L = lanes[waiter % n_lanes]; { std::lock_guard<std::mutex> l(L.m); f[i] = 1; } L.cv.notify_one(); }
+  void wait(size_t i, size_t me, const std::atomic<int>& err) {
+    Lane& L = lanes[me % n_lanes];
+    std::unique_lock<std::mutex> l(L.m);
+    L.cv.wait(l, [&] { return f[i] || err.load(); });
+  }
+  void wake() { for (size_t k = 0; k < n_lanes; ++k) { { std::lock_guard<std::mutex> l(lanes[k].m); } lanes[k].cv.notify_all(); } }
 };
 
 }  // namespace
@@ -127,20 +139,20 @@ static void seq_work(dms_sequence* s, int k) {
       if (!rc) rc = dms_odom_init_rgb_model(h, fmi, 0, st);
       if (!rc) rc = dms_odom_init_icp_depth(h, fd, 0, o.depthCutoff, st);
       if (!rc) {
-        if (K > 1) s->taken.wait((size_t)i, err);
+        if (K > 1) s->taken.wait((size_t)i, (size_t)k, err);
         rc = dms_odom_init_rgb(h, fli, 0, st);
       }
-      s->issued.set((size_t)i);
+      s->issued.set((size_t)i, (size_t)(i + 1) % K);        // waited for by the thread of frame i + 1
       if (!rc) {
         if (i == 0 || K == 1) {
           // one tracker keeps its own previous image (RO.cpp:595-601); the first frame loads the one it is given
           if (i == 0) rc = host ? dms_odom_init_first_rgb_host(h, first_prev, 0, st) : dms_odom_init_first_rgb(h, first_prev, 0, st);
         } else {
-          s->issued.wait((size_t)i - 1, err);
+          s->issued.wait((size_t)i - 1, (size_t)k, err);
           if (!err.load()) rc = dms_odom_init_first_rgb_from(h, s->trk[(i - 1) % K], st);
         }
       }
-      s->taken.set((size_t)i - 1 + K);
+      s->taken.set((size_t)i - 1 + K, (size_t)(i - 1 + K) % K);   // waited for by the thread of frame i - 1 + K
       float trans[3] = {f.prior[3], f.prior[7], f.prior[11]};
       float rot[9] = {f.prior[0], f.prior[1], f.prior[2], f.prior[4], f.prior[5], f.prior[6], f.prior[8], f.prior[9], f.prior[10]};
       if (!rc) rc = dms_odom_track_async(h, trans, rot, o.rgbOnly, o.icpWeight, o.pyramid, o.fastOdom, o.so3, 0, st);
@@ -249,9 +261,9 @@ int dms_sequence_resident(const dms_sequence* s) { return s ? s->resident : 0; }
 int dms_sequence_run(dms_sequence* s, const dms_seq_frame* frames, int n, const uint8_t* first_prev, int host, dms_seq_result* out) {
   if (!s || !frames || !out || n < 0 || (n > 0 && !first_prev)) return DMS_ERR_INVALID;
   const int K = (int)s->trk.size();
-  s->issued.reset((size_t)n + 1);
-  s->taken.reset((size_t)n + K + 1);
-  for (int j = 0; j < K; ++j) s->taken.set((size_t)j);
+  s->issued.reset((size_t)n + 1, (size_t)K);
+  s->taken.reset((size_t)n + K + 1, (size_t)K);
+  for (int j = 0; j < K; ++j) s->taken.set((size_t)j, (size_t)j);
   s->err.store(0);
   s->t_entry = std::chrono::steady_clock::now(); s->t_first_launch_us.store(-1); s->t_last_collect_us.store(0);
   s->job.frames = frames; s->job.n = n; s->job.first_prev = first_prev; s->job.host = host; s->job.out = out;
