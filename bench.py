@@ -472,6 +472,7 @@ def main():
         so3_seen = [r.r.so3_iters for r in res]
         pose = np.array(res[steps - 1].pose[:], np.float32).reshape(4, 4)
         timed_native.last_result = res[steps - 1].r
+        timed_native.host_ms = [float(r.host_ms) for r in res]
         return ms, ktimes, iters_seen, so3_seen, clocks, (pose[:3, 3].copy(), pose[:3, :3].copy())
 
     def timed(pipe, steps, warmup, host):
@@ -633,11 +634,24 @@ def main():
         # caller sees, ElasticFusion.cpp:173-201: the model view of frame f+1 exists only after frame f is fused).  Every
         # rank measures it on its own GPU; rank 0 reports its own numbers.
         del pipe, seq
-        pipe1 = make_pipe(1)
         n1 = min(args.steps, 300)
-        ms1, k1, it1, s31, _, _ = timed(pipe1, n1, args.warmup, False)
-        lat = np.sort(np.array(timed.latencies))
-        track_us = float(np.mean([p_["track"] for p_ in timed.phases])) * 1e3
+        if native:
+            # the library's own runner with one tracker (frames strictly one after another, its host side in C++): what a
+            # C / C++ caller of the library sees; per-frame host latency = first init call of the frame -> result in hand
+            from densemonoslam_b200.sequence import SequenceTracker
+            seq1 = SequenceTracker(cam.width, cam.height, cam.cx, cam.cy, cam.fx, cam.fy, device=local_rank, n_trackers=1, block_threads=0, grid=0, wait_mode=0,
+                                   rgbOnly=int(FLAGS["rgbOnly"]), icpWeight=FLAGS["icpWeight"], pyramid=int(FLAGS["pyramid"]), fastOdom=int(FLAGS["fastOdom"]),
+                                   so3=int(FLAGS["so3"]), depthCutoff=25.0, timing=3)
+            ms1, k1, it1, s31, _, _ = timed_native(seq1, n1, args.warmup, False)
+            lat = np.sort(np.array(timed_native.host_ms))
+            track_us = float(np.mean(k1)) * 1e3
+            del seq1
+            pipe1 = make_pipe(1)
+        else:
+            pipe1 = make_pipe(1)
+            ms1, k1, it1, s31, _, _ = timed(pipe1, n1, args.warmup, False)
+            lat = np.sort(np.array(timed.latencies))
+            track_us = float(np.mean([p_["track"] for p_ in timed.phases])) * 1e3
         # phase breakdown: a short second run on the instrumented build of the kernel (about 3 % slower), outside the numbers above
         pipe1[0][0].set_timing(1)
         timed(pipe1, min(n1, 40), 3, False)
@@ -645,7 +659,7 @@ def main():
         ph["track_instrumented"] = ph.get("track"); ph["track"] = track_us
         gn_its = max(1, int(np.mean([sum(it) for it in it1])))
         out["latency"] = {"value": world * n1 / (ms1 * 1e-3), "unit": "frames/s", "ms_per_frame": ms1 / n1, "frames": n1,
-                          "mode": "one tracker per GPU, one frame in flight, inputs resident in HBM",
+                          "mode": "one tracker per GPU, one frame in flight, inputs resident in HBM; driven by " + ("dms_sequence_run with one tracker" if native else "Python over the per-call C ABI"),
                           "host_latency_ms": {"p50": float(lat[len(lat) // 2]), "p99": float(lat[min(len(lat) - 1, int(len(lat) * 0.99))]),
                                               "max": float(lat[-1]), "frames": int(len(lat))},
                           "track_us": ph.get("track"), "phase_us": ph,

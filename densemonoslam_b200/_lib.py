@@ -64,7 +64,7 @@ class DmsSeqFrame(C.Structure):
 
 
 class DmsSeqResult(C.Structure):
-    _fields_ = [("pose", C.c_float * 16), ("r", DmsResult), ("track_ms", C.c_float)]
+    _fields_ = [("pose", C.c_float * 16), ("r", DmsResult), ("track_ms", C.c_float), ("host_ms", C.c_float)]
 
 
 class DmsRingRecord(C.Structure):

@@ -453,12 +453,22 @@ int dms_odom_track_collect(dms_odom* h, float trans[3], float rot[9], void* stre
   h->in_flight = 0;
   if (h->blocking_wait >= 2) {
     const auto t0 = std::chrono::steady_clock::now();
-    if (h->wait_ema_us > 150.0) std::this_thread::sleep_for(std::chrono::nanoseconds((long long)(h->wait_ema_us * 850.0)));
-    while ((e = cudaEventQuery(h->ev_done)) == cudaErrorNotReady) {
-      if (h->blocking_wait == 3) std::this_thread::sleep_for(std::chrono::microseconds(20)); else sched_yield();
+    const bool slept = h->wait_ema_us > 150.0;
+    if (slept) std::this_thread::sleep_for(std::chrono::nanoseconds((long long)(h->wait_ema_us * 850.0)));
+    e = cudaEventQuery(h->ev_done);
+    if (slept && e != cudaErrorNotReady) {
+      // the result was already there when the sleep ended: the estimate is too long by an unknown amount.  Measuring
+      // this wait would only return the sleep itself, so one long wait (the first frame of a run waits for its uploads)
+      // kept the estimate high for dozens of frames and every later result was collected late: shrink it instead.
+      h->wait_ema_us *= 0.7;
+    } else {
+      while (e == cudaErrorNotReady) {
+        if (h->blocking_wait == 3) std::this_thread::sleep_for(std::chrono::microseconds(20)); else sched_yield();
+        e = cudaEventQuery(h->ev_done);
+      }
+      const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+      h->wait_ema_us = h->wait_ema_us == 0.0 ? us : 0.8 * h->wait_ema_us + 0.2 * us;
     }
-    const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
-    h->wait_ema_us = h->wait_ema_us == 0.0 ? us : 0.8 * h->wait_ema_us + 0.2 * us;
   } else if (h->blocking_wait == 1) {
     e = cudaEventSynchronize(h->ev_done);
   } else {

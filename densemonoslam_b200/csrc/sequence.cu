@@ -126,6 +126,7 @@ static void seq_work(dms_sequence* s, int k) {
       const dms_seq_frame& f = frames[i];
       const Stage* cur = nullptr;
       int rc = DMS_OK;
+      const std::chrono::steady_clock::time_point t_frame = std::chrono::steady_clock::now();
       if (host) {
         Stage& c = sg[(i / K) & 1];
         if (c.frame != i) rc = upload(i, c);
@@ -176,6 +177,7 @@ static void seq_work(dms_sequence* s, int k) {
       dms_odom_timing tm;
       dms_odom_get_timing(h, &tm);
       out[i].track_ms = tm.track_ms;
+      out[i].host_ms = (float)(std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t_frame).count() * 1e-6);
     }
   }
 }

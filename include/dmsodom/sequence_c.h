@@ -29,6 +29,8 @@ typedef struct dms_seq_result {
   float pose[16];             /* refined pose, row-major */
   dms_odom_result r;
   float track_ms;             /* device time of the tracking kernel of this frame (options.timing != 0) */
+  float host_ms;              /* host-visible latency of this frame: from its first init call to its result in hand (with several
+                                 trackers this includes the waits for the image hand-off between them) */
 } dms_seq_result;
 
 typedef struct dms_seq_options {
