@@ -281,11 +281,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti")
     ap.add_argument("--ring", type=int, default=8, help="distinct frames kept resident (must exceed L2 in total)")
-    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 20, fewer for short runs so that every tracker gets two frames or more)")
+    ap.add_argument("--pipeline", type=int, default=0, help="trackers sharing the GPU concurrently (1 = strictly sequential frames; 0 = auto: 20, fewer when the run has fewer frames)")
     ap.add_argument("--threads", type=int, default=512, help="threads per block of the tracking kernel when trackers share the GPU (0 = library default, 768)")
     ap.add_argument("--grid", type=int, default=0, help="thread blocks per tracking kernel (default: SMs / pipeline depth)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--wait", type=int, default=-1, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep then poll + yield, 3 sleep then poll + 20 us sleeps; default: 2, or 3 when the ranks of this box have more tracker threads than host cores")
+    ap.add_argument("--wait", type=int, default=-1, help="how pipelined trackers wait for a result: 0 spin, 1 blocking event, 2 sleep then poll + yield, 3 sleep then poll + 20 us sleeps; default: 2, or 3 when the ranks of this box have more than two tracker threads per host core")
     ap.add_argument("--driver", default="native", choices=["native", "python"], help="who runs the trackers' host threads when they share the GPU: the library's sequence runner or Python threads")
     ap.add_argument("--no-share-rgb", action="store_true", help="pipelined trackers reload the previous frame's image instead of taking its pyramid from the tracker that has it")
     ap.add_argument("--quick", action="store_true", help="tuning runs: only the device-resident leg")
@@ -293,7 +293,9 @@ def main():
 
     if args.wait < 0:
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
-        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else min(20, max(2, args.steps // 2))) > len(os.sched_getaffinity(0)) else 2
+        # sleep-then-poll with short sleeps only when the box is heavily oversubscribed (more than two tracker threads per core);
+        # twenty yielding pollers on sixteen cores were measured faster than twenty 20-us sleepers
+        args.wait = 3 if local_world * max(1, args.pipeline if args.pipeline else min(20, max(2, args.steps))) > 2 * len(os.sched_getaffinity(0)) else 2
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -552,10 +554,10 @@ def main():
                 "kernel_share_of_step": (k_ms / depth) / (ms / steps),
                 "us_per_gn_iteration": 1000.0 * k_ms / max(1, int(np.mean([sum(it) for it in iters_seen])))}
 
-    # trackers sharing the GPU: 20 in a long run (measured, tools/quick_perf.py at 300 frames: 12 x 24 blocks 5500 frames/s,
-    # 20 x 14 blocks 5900, 28 x 10 5950); a short run (the driver's 20 steps) fills and drains the pipeline once, which costs
-    # less with fewer, larger trackers that get two frames each (10 x 29: 5080 at 20 frames, 20 x 14: 4300 - 5300)
-    depth = max(1, args.pipeline) if args.pipeline else min(20, max(2, args.steps // 2))
+    # trackers sharing the GPU: 20 (measured, tools/quick_perf.py at 300 frames: 12 x 24 blocks 5500 frames/s, 20 x 14 blocks
+    # 5900, 28 x 10 5950), also in the driver's 20-step run, where every tracker then gets one frame (20 x 14: 5350 - 5440
+    # frames/s at 20 frames, 10 x 29: 5150; 8 GPUs: 38 050 against 35 760 - 36 930)
+    depth = max(1, args.pipeline) if args.pipeline else min(20, max(2, args.steps))
     depth_e2e = max(1, args.pipeline) if args.pipeline else min(6, max(2, args.steps // 5))   # uploads inside the region: PCIe-bound, fewer trackers start sooner
     _thr = args.threads if args.threads else 768
     _queues = int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8"))
