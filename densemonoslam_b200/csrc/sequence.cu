@@ -15,29 +15,7 @@
 #include <cuda_runtime.h>
 #include "../../include/dmsodom/sequence_c.h"
 #include "../../include/dmsodom/ring_c.h"
-
-namespace {
-
-// Monotone per-frame flags.  Every flag has exactly one waiter (the thread of the tracker that needs it), so each tracker
-// thread owns a mutex / condition variable pair and a setter wakes that thread alone: with one shared condition variable
-// every set woke all the trackers' threads, which hurts when the ranks of a box have more tracker threads than cores.
-struct Flags {
-  struct Lane { std::mutex m; std::condition_variable cv; };
-  std::unique_ptr<Lane[]> lanes; size_t n_lanes = 0; std::vector<char> f;
-  void reset(size_t n, size_t k) {
-    if (k != n_lanes) { lanes.reset(new Lane[k]); n_lanes = k; }
-    f.assign(n, 0);   // no run is in progress: the workers are parked
-  }
-  void set(size_t i, size_t waiter) { Lane& L = lanes[waiter % n_lanes]; { std::lock_guard<std::mutex> l(L.m); f[i] = 1; } L.cv.notify_one(); }
-  void wait(size_t i, size_t me, const std::atomic<int>& err) {
-    Lane& L = lanes[me % n_lanes];
-    std::unique_lock<std::mutex> l(L.m);
-    L.cv.wait(l, [&] { return f[i] || err.load(); });
-  }
-  void wake() { for (size_t k = 0; k < n_lanes; ++k) { { std::lock_guard<std::mutex> l(lanes[k].m); } lanes[k].cv.notify_all(); } }
-};
-
-}  // namespace
+#include "seq_flags.h"
 
 // Device-side copy of one frame's inputs (host-buffer runs): a tracker owns two of them and a copy stream, so the upload of
 // its NEXT frame (frame i + K) runs under the kernels of the current one and the PCIe link always has a copy queued.
@@ -58,7 +36,7 @@ struct dms_sequence {
   std::vector<Stage> stages;   // two per tracker, allocated by the first host-buffer run
   int grid, resident;
   dms_ring* ring = nullptr; int ring_sensor = 0;   // results of every tracked frame also go to this ring (dms_sequence_attach_ring)
-  Flags issued, taken;
+  dms_seq::Flags issued, taken;
   // worker pool: one host thread per tracker, created once and parked between runs (spawning them per run cost a
   // fixed ~2 ms per call, which dominated short runs and multi-rank launches)
   std::vector<std::thread> workers;
